@@ -1,0 +1,155 @@
+"""ctypes bindings for the CPU oracle — TEST INFRASTRUCTURE.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl
+reference`` legs may import this module.  Two back ends with the same interface:
+
+* ``kind="reference"`` — ``oracle/_ref/libsplat_ref.so``: the reference's own code
+  (codelets/splat/codelets.cpp + include/splat/*.hpp), compiled by ``oracle/build_ref.sh``.
+* ``kind="port"``      — ``oracle/liboracle.so``: the plain-C restatement ``splat_oracle.c``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from dataclasses import dataclass
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_SO = os.path.join(HERE, "_ref", "libsplat_ref.so")
+PORT_SO = os.path.join(HERE, "liboracle.so")
+REF_DATA = os.path.join(HERE, "_ref", "data")
+
+_fp = C.POINTER(C.c_float)
+
+
+def build_port() -> str:
+    if not os.path.exists(PORT_SO) or os.path.getmtime(PORT_SO) < os.path.getmtime(os.path.join(HERE, "splat_oracle.c")):
+        subprocess.run(["make", "-C", HERE, "liboracle.so"], check=True, capture_output=True)
+    return PORT_SO
+
+
+def build_ref() -> str | None:
+    """Build oracle/_ref from /root/reference when it is present (this container only)."""
+    if os.path.isdir("/root/reference/codelets"):
+        subprocess.run([os.path.join(HERE, "build_ref.sh")], check=True, capture_output=True)
+    return REF_SO if os.path.exists(REF_SO) else None
+
+
+def have_ref() -> bool:
+    return os.path.exists(REF_SO)
+
+
+@dataclass
+class Frame:
+    rec: np.ndarray        # (n,8) px,py,clip_z,cov_a,cov_b,cov_c,radius,drawn
+    rect: np.ndarray       # (n,4) c0,c1,r0,r1
+    counts: np.ndarray     # (tiles,) u32
+    offsets: np.ndarray    # (tiles+1,) i64
+    lists: np.ndarray      # (D,) i32 gaussian index, per tile in (z asc, index asc) order
+    fb: np.ndarray | None  # (W*H*4,) f32 tile-major
+    ms: tuple              # project, bin, blend (CPU milliseconds)
+    pairs: int = 0
+
+    @property
+    def drawn(self) -> np.ndarray:
+        return self.rec[:, 7] > 0
+
+
+class Oracle:
+    def __init__(self, kind: str = "port"):
+        if kind == "reference":
+            if not os.path.exists(REF_SO):
+                raise FileNotFoundError(REF_SO)
+            path, self.p = REF_SO, "ref_"
+        elif kind == "port":
+            path, self.p = build_port(), "orc_"
+        else:
+            raise ValueError(kind)
+        self.kind = kind
+        self.lib = C.CDLL(path)
+        f = self._fn
+        f("frame_create", C.c_void_p, [_fp, C.c_size_t, _fp, _fp, C.c_float, C.c_float] + [C.c_int] * 6)
+        f("frame_destroy", None, [C.c_void_p])
+        f("frame_num_duplicates", C.c_size_t, [C.c_void_p])
+        f("frame_get_records", None, [C.c_void_p, _fp, C.POINTER(C.c_int32)])
+        f("frame_get_lists", None, [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_int64), C.POINTER(C.c_int32)])
+        f("frame_get_framebuffer", None, [C.c_void_p, _fp])
+        f("frame_get_timings", None, [C.c_void_p, C.POINTER(C.c_double)])
+        f("num_threads", C.c_int, [])
+        f("conic_opacity", None, [_fp, C.c_float, _fp])
+        f("tile_bounds", None, [C.c_int] * 4 + [C.c_uint, _fp])
+        if kind == "port":
+            f("frame_num_pairs", C.c_uint64, [C.c_void_p])
+            f("framebuffer_to_bgr8", None, [_fp] + [C.c_int] * 4 + [C.POINTER(C.c_uint8)])
+
+    def _fn(self, name, res, args):
+        fn = getattr(self.lib, self.p + name)
+        fn.restype, fn.argtypes = res, args
+        setattr(self, "_" + name, fn)
+
+    @property
+    def cores(self) -> int:
+        return int(self._num_threads())
+
+    def frame(self, g16, view, proj, fov, scale_div, W, H, tile_w=32, tile_h=20, render=True, threads=0) -> Frame:
+        g16 = np.ascontiguousarray(g16, dtype=np.float32).reshape(-1, 16)
+        view = np.ascontiguousarray(view, dtype=np.float32).ravel()
+        proj = np.ascontiguousarray(proj, dtype=np.float32).ravel()
+        n = g16.shape[0]
+        TA, TD = W // tile_w, H // tile_h
+        assert TA * tile_w == W and TD * tile_h == H
+        h = self._frame_create(g16.ctypes.data_as(_fp), n, view.ctypes.data_as(_fp), proj.ctypes.data_as(_fp),
+                               fov, scale_div, W, H, TA, TD, int(render), threads)
+        try:
+            D = int(self._frame_num_duplicates(h))
+            rec = np.empty((n, 8), np.float32)
+            rect = np.empty((n, 4), np.int32)
+            self._frame_get_records(h, rec.ctypes.data_as(_fp), rect.ctypes.data_as(C.POINTER(C.c_int32)))
+            counts = np.empty(TA * TD, np.uint32)
+            offsets = np.empty(TA * TD + 1, np.int64)
+            lists = np.empty(max(D, 1), np.int32)
+            self._frame_get_lists(h, counts.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                  offsets.ctypes.data_as(C.POINTER(C.c_int64)),
+                                  lists.ctypes.data_as(C.POINTER(C.c_int32)))
+            fb = None
+            if render:
+                fb = np.empty(W * H * 4, np.float32)
+                self._frame_get_framebuffer(h, fb.ctypes.data_as(_fp))
+            ms = (C.c_double * 3)()
+            self._frame_get_timings(h, ms)
+            pairs = int(self._frame_num_pairs(h)) if self.kind == "port" else 0
+        finally:
+            self._frame_destroy(h)
+        return Frame(rec, rect, counts, offsets, lists[:D], fb, tuple(ms), pairs)
+
+    def conic_opacity(self, cov, opacity):
+        cov = np.ascontiguousarray(cov, np.float32)
+        out = np.empty(4, np.float32)
+        self._conic_opacity(cov.ctypes.data_as(_fp), opacity, out.ctypes.data_as(_fp))
+        return out
+
+    def tile_bounds(self, W, H, TA, TD, tid):
+        out = np.empty(4, np.float32)
+        self._tile_bounds(W, H, TA, TD, tid, out.ctypes.data_as(_fp))
+        return out
+
+    def to_bgr8(self, fb, W, H, tile_w=32, tile_h=20):
+        assert self.kind == "port"
+        fb = np.ascontiguousarray(fb, np.float32)
+        out = np.empty((H, W, 3), np.uint8)
+        self._framebuffer_to_bgr8(fb.ctypes.data_as(_fp), W, H, W // tile_w, H // tile_h,
+                                  out.ctypes.data_as(C.POINTER(C.c_uint8)))
+        return out
+
+
+def detile(fb_tiled: np.ndarray, W: int, H: int, tile_w=32, tile_h=20) -> np.ndarray:
+    """tile-major f32 chunks -> (H, W, 4) image (layout of ipu_rasteriser.cpp:115-129)."""
+    TA, TD = W // tile_w, H // tile_h
+    return (fb_tiled.reshape(TD, TA, tile_h, tile_w, 4).transpose(0, 2, 1, 3, 4).reshape(H, W, 4))
+
+
+def psnr(a: np.ndarray, b: np.ndarray, peak: float = 1.0) -> float:
+    mse = float(np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2))
+    return float("inf") if mse == 0 else 10.0 * np.log10(peak * peak / mse)
