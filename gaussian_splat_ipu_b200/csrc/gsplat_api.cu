@@ -1,0 +1,263 @@
+// gsplat_api.cu — the C ABI of libgsplat_b200.so (include/gsplat_b200.h): context, memory, the
+// per-frame stage sequence K1 -> scan -> K2 -> K3 -> K4 -> K5, read-back.  Host side of what
+// splat::IpuSplatter + ipu_utils::GraphManager do for the reference
+// (src/splat/ipu_rasteriser.cpp:49-144,250-420; include/ipu/ipu_utils.hpp:523-623).
+#include "../../include/gsplat_b200.h"
+#include "gsplat_internal.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace gsplat;
+
+namespace {
+thread_local std::string g_create_error;
+
+enum Ev { EV_START = 0, EV_K1, EV_SCAN, EV_K2, EV_K3, EV_K4, EV_K5, EV_POST0, EV_POST1, EV_COUNT };
+}  // namespace
+
+struct gsplat_ctx {
+  gsplat_config cfg{};
+  cudaStream_t st = nullptr;
+  std::string err;
+  int tiles_across = 0, tiles_down = 0, num_tiles = 0;
+  // scene
+  SceneSoA scene{};
+  // per-Gaussian frame buffers
+  Projected proj{};
+  uint32_t *block_sums = nullptr;
+  uint32_t n_blocks = 0;
+  float *dbg_rec8 = nullptr;
+  int32_t *dbg_rect4 = nullptr;
+  // device scalars: [0] D  [1] V  [2] overflow
+  uint32_t *d_scalars = nullptr;
+  uint32_t *h_scalars = nullptr;   // pinned mirror
+  // duplicates
+  SortBuffers sort{};
+  int sorted = 0;                  // which of sort.keys/vals holds the sorted result
+  uint2 *ranges = nullptr;
+  uint32_t *counts = nullptr;
+  float4 *fb = nullptr;
+  uint8_t *bgr = nullptr;
+  // state
+  FrameParams fp{};
+  bool have_scene = false, have_camera = false, have_frame = false;
+  gsplat_frame_stats stats{};
+  cudaEvent_t ev[EV_COUNT]{};
+  bool post_timed = false;
+  int key_bits = 0;
+};
+
+namespace {
+
+int fail(gsplat_ctx *c, int code, const std::string &msg) {
+  if (c) c->err = msg; else g_create_error = msg;
+  return code;
+}
+
+#define CU(call)                                                                                  \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess)                                                                        \
+      return fail(ctx, GSPLAT_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));        \
+  } while (0)
+
+template <typename T> void dfree(T *&p) { if (p) { cudaFree(p); p = nullptr; } }
+
+void free_sort(SortBuffers &s) {
+  dfree(s.keys[0]); dfree(s.keys[1]); dfree(s.vals[0]); dfree(s.vals[1]); dfree(s.block_hist); dfree(s.digit_base);
+  s.capacity = 0; s.max_blocks = 0;
+}
+
+int alloc_sort(gsplat_ctx *ctx, size_t capacity) {
+  if (capacity > 0xfffff000ull) return fail(ctx, GSPLAT_E_CAPACITY, "duplicate count exceeds 32-bit indexing");
+  cudaSetDevice(ctx->cfg.device);
+  free_sort(ctx->sort);
+  SortBuffers &s = ctx->sort;
+  capacity = (capacity + RS_TILE - 1) / RS_TILE * RS_TILE;
+  s.max_blocks = (uint32_t)(capacity / RS_TILE);
+  for (int i = 0; i < 2; ++i) {
+    CU(cudaMalloc(&s.keys[i], capacity * sizeof(uint64_t)));
+    CU(cudaMalloc(&s.vals[i], capacity * sizeof(uint32_t)));
+  }
+  CU(cudaMalloc(&s.block_hist, (size_t)256 * s.max_blocks * sizeof(uint32_t)));
+  CU(cudaMalloc(&s.digit_base, 256 * sizeof(uint32_t)));
+  s.capacity = (uint32_t)capacity;
+  return GSPLAT_OK;
+}
+
+int ceil_log2(uint32_t v) { int b = 0; while ((1u << b) < v) ++b; return b; }
+
+// glm type_mat4x4.inl:630-648, left-to-right sums; column-major 16-float arrays
+void mat4_mul(const float *a, const float *b, float *r) {
+  for (int c = 0; c < 4; ++c)
+    for (int k = 0; k < 4; ++k)
+      r[c * 4 + k] = ((a[0 + k] * b[c * 4 + 0] + a[4 + k] * b[c * 4 + 1]) + a[8 + k] * b[c * 4 + 2]) +
+                     a[12 + k] * b[c * 4 + 3];
+}
+
+}  // namespace
+
+extern "C" {
+
+int gsplat_abi_version(void) { return GSPLAT_ABI_VERSION; }
+
+int gsplat_config_default(gsplat_config *cfg) {
+  if (!cfg) return GSPLAT_E_ARG;
+  std::memset(cfg, 0, sizeof *cfg);
+  cfg->device = 0;
+  cfg->width = 1280; cfg->height = 720;      // tile_config.hpp:5-6
+  cfg->tile_w = 32; cfg->tile_h = 20;        // tile_config.hpp:9-15 (1280/40, 720/36)
+  cfg->guard_factor = 15.0f;                 // codelets.cpp:622
+  return GSPLAT_OK;
+}
+
+const char *gsplat_last_error(const gsplat_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+void gsplat_destroy(gsplat_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->cfg.device);
+  if (ctx->st) cudaStreamSynchronize(ctx->st);
+  dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
+  dfree(ctx->proj.a); dfree(ctx->proj.b); dfree(ctx->proj.c); dfree(ctx->proj.touched);
+  dfree(ctx->block_sums); dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->d_scalars);
+  free_sort(ctx->sort);
+  dfree(ctx->ranges); dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
+  if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
+  for (auto &e : ctx->ev) if (e) cudaEventDestroy(e);
+  if (ctx->st) cudaStreamDestroy(ctx->st);
+  delete ctx;
+}
+
+int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
+  gsplat_ctx *ctx = nullptr;
+  if (!cfg || !out) return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: null argument");
+  *out = nullptr;
+  if (cfg->width <= 0 || cfg->height <= 0 || cfg->tile_w <= 0 || cfg->tile_h <= 0 ||
+      cfg->width % cfg->tile_w || cfg->height % cfg->tile_h)
+    return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: tile size must divide the image size");
+  if (cfg->tile_w != 32 || cfg->tile_h % 4 || cfg->tile_h > 32)
+    return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: K5 supports tile_w == 32 and tile_h in {4,8,...,32}");
+  if (cfg->width / cfg->tile_w > 65535 || cfg->height / cfg->tile_h > 65535)
+    return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: tile grid exceeds 16-bit tile coordinates");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(nullptr, GSPLAT_E_CUDA, std::string("gsplat_create: no CUDA device (there is no CPU fallback): ") +
+                                            cudaGetErrorString(e));
+  if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: bad device ordinal");
+  ctx = new gsplat_ctx;
+  ctx->cfg = *cfg;
+  ctx->tiles_across = cfg->width / cfg->tile_w;
+  ctx->tiles_down = cfg->height / cfg->tile_h;
+  ctx->num_tiles = ctx->tiles_across * ctx->tiles_down;
+  if (ctx->cfg.band_row_begin == 0 && ctx->cfg.band_row_end == 0) ctx->cfg.band_row_end = ctx->tiles_down;
+  if (ctx->cfg.band_row_begin < 0 || ctx->cfg.band_row_end > ctx->tiles_down ||
+      ctx->cfg.band_row_begin > ctx->cfg.band_row_end) {
+    delete ctx;
+    return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: bad tile-row band");
+  }
+#define CUC(call)                                                                                  \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      std::string m_ = std::string(#call) + ": " + cudaGetErrorString(e_);                         \
+      gsplat_destroy(ctx);                                                                         \
+      return fail(nullptr, GSPLAT_E_CUDA, m_);                                                     \
+    }                                                                                              \
+  } while (0)
+  CUC(cudaSetDevice(cfg->device));
+  CUC(cudaStreamCreateWithFlags(&ctx->st, cudaStreamNonBlocking));
+  for (auto &ev : ctx->ev) CUC(cudaEventCreate(&ev));
+  CUC(cudaMalloc(&ctx->d_scalars, 16 * sizeof(uint32_t)));
+  CUC(cudaMemset(ctx->d_scalars, 0, 16 * sizeof(uint32_t)));
+  CUC(cudaHostAlloc(&ctx->h_scalars, 16 * sizeof(uint32_t), cudaHostAllocDefault));
+  const size_t px = (size_t)cfg->width * cfg->height;
+  CUC(cudaMalloc(&ctx->ranges, sizeof(uint2) * ctx->num_tiles));
+  CUC(cudaMalloc(&ctx->counts, sizeof(uint32_t) * ctx->num_tiles));
+  CUC(cudaMalloc(&ctx->fb, sizeof(float4) * px));
+  CUC(cudaMalloc(&ctx->bgr, px * 3));
+  CUC(cudaMemset(ctx->fb, 0, sizeof(float4) * px));
+  CUC(cudaMemset(ctx->bgr, 0, px * 3));
+  CUC(cudaMemset(ctx->counts, 0, sizeof(uint32_t) * ctx->num_tiles));
+  CUC(cudaMemset(ctx->ranges, 0, sizeof(uint2) * ctx->num_tiles));
+#undef CUC
+  *out = ctx;
+  return GSPLAT_OK;
+}
+
+int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
+  if (!ctx || (!g16 && n)) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: null argument");
+  if (n > 0x7fffffffull) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: too many Gaussians");
+  CU(cudaSetDevice(ctx->cfg.device));
+  CU(cudaStreamSynchronize(ctx->st));
+  dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
+  dfree(ctx->proj.a); dfree(ctx->proj.b); dfree(ctx->proj.c); dfree(ctx->proj.touched);
+  dfree(ctx->block_sums); dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4);
+  ctx->have_scene = ctx->have_frame = false;
+  const size_t na = n ? n : 1;
+  ctx->scene.n = (uint32_t)n;
+  CU(cudaMalloc(&ctx->scene.pos_s0, na * sizeof(float4)));
+  CU(cudaMalloc(&ctx->scene.quat, na * sizeof(float4)));
+  CU(cudaMalloc(&ctx->scene.rgba, na * sizeof(float4)));
+  CU(cudaMalloc(&ctx->scene.s12, na * sizeof(float2)));
+  CU(cudaMalloc(&ctx->proj.a, na * sizeof(float4)));
+  CU(cudaMalloc(&ctx->proj.b, na * sizeof(float4)));
+  CU(cudaMalloc(&ctx->proj.c, na * sizeof(float4)));
+  CU(cudaMalloc(&ctx->proj.touched, na * sizeof(uint32_t)));
+  CU(cudaMemsetAsync(ctx->proj.c, 0, na * sizeof(float4), ctx->st));
+  ctx->n_blocks = (uint32_t)((n + K1_THREADS - 1) / K1_THREADS);
+  CU(cudaMalloc(&ctx->block_sums, (ctx->n_blocks + 1) * sizeof(uint32_t)));
+  if (ctx->cfg.debug_records) {
+    CU(cudaMalloc(&ctx->dbg_rec8, na * 8 * sizeof(float)));
+    CU(cudaMalloc(&ctx->dbg_rect4, na * 4 * sizeof(int32_t)));
+  }
+  if (n) {
+    // stage the AoS records in the (not yet needed) projected buffers' place: one temporary
+    float *tmp = nullptr;
+    CU(cudaMalloc(&tmp, n * 16 * sizeof(float)));
+    cudaError_t e = cudaMemcpyAsync(tmp, g16, n * 16 * sizeof(float), cudaMemcpyHostToDevice, ctx->st);
+    if (e == cudaSuccess) {
+      launch_aos_to_soa(tmp, ctx->scene, ctx->st);
+      e = cudaStreamSynchronize(ctx->st);
+    }
+    cudaFree(tmp);
+    if (e != cudaSuccess) return fail(ctx, GSPLAT_E_CUDA, std::string("scene upload: ") + cudaGetErrorString(e));
+  }
+  if (ctx->sort.capacity == 0) {
+    size_t cap = ctx->cfg.dup_capacity ? ctx->cfg.dup_capacity : (n * 3 + (size_t)RS_TILE);
+    int rc = alloc_sort(ctx, cap);
+    if (rc) return rc;
+  }
+  ctx->have_scene = true;
+  return GSPLAT_OK;
+}
+
+int gsplat_set_camera(gsplat_ctx *ctx, const float mv[16], const float proj[16], float fov, float scale_div) {
+  if (!ctx || !mv || !proj) return fail(ctx, GSPLAT_E_ARG, "gsplat_set_camera: null argument");
+  FrameParams &fp = ctx->fp;
+  // codelets.cpp:443: mvp = projmatrix * viewmatrix (the host-side transpose of
+  // ipu_rasteriser.cpp:86-102 and the codelet's transpose back, :625-628, cancel)
+  mat4_mul(proj, mv, fp.mvp);
+  // codelets.cpp:444-448: tan(0.5*fxy[0]) is a double expression narrowed to float; the focal
+  // lengths use glm::tan on floats; tfb.width/height are uint16 (tile_config.hpp:22-31)
+  fp.tanfov = (float)std::tan(0.5 * (double)fov);
+  fp.focal_x = (float)(uint16_t)ctx->cfg.width / (2.f * std::tan(fov / 2.f));
+  fp.focal_y = (float)(uint16_t)ctx->cfg.height / (2.f * std::tan(fov / 2.f));
+  fp.scale_div = scale_div;
+  fp.img_w = (float)ctx->cfg.width; fp.img_h = (float)ctx->cfg.height;
+  fp.tile_w = (float)ctx->cfg.tile_w; fp.tile_h = (float)ctx->cfg.tile_h;
+  // tb.diagonal().length() * clipSize (codelets.cpp:470,622; ipu_geometry.hpp:53-55,116-118)
+  fp.guard = std::sqrt(fp.tile_w * fp.tile_w + fp.tile_h * fp.tile_h) * ctx->cfg.guard_factor;
+  fp.tiles_across = ctx->tiles_across; fp.tiles_down = ctx->tiles_down;
+  fp.row_begin = ctx->cfg.band_row_begin; fp.row_end = ctx->cfg.band_row_end;
+  ctx->have_camera = true;
+  return GSPLAT_OK;
+}
+
+}  // extern "C"
+
+#include "gsplat_api_frame.inc"

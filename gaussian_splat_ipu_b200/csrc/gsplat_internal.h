@@ -1,0 +1,92 @@
+// gsplat_internal.h — shared declarations of the sm_100a kernels behind libgsplat_b200.so.
+// Stage names follow SURVEY.md §8: K1 project, (scan), K2 duplicate, K3 sort, K4 ranges, K5 blend.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+namespace gsplat {
+
+// Per-frame constants, computed once on the host exactly as GSplat::renderInternal does
+// (codelets/splat/codelets.cpp:443-448,470,622-628) and passed to K1 by value.
+struct FrameParams {
+  float mvp[16];     // projection * modelview, glm column-major: mvp[c*4+r]
+  float tanfov;      // (float)tan(0.5*fov): used for BOTH axes (codelets.cpp:444-445)
+  float focal_x, focal_y;
+  float scale_div;   // fxy[1]
+  float img_w, img_h;
+  float tile_w, tile_h;
+  float guard;       // |tile diagonal| * clipSize
+  int tiles_across, tiles_down;
+  int row_begin, row_end;   // tile-row band rendered by this context
+};
+
+// Scene in HBM: exactly the 56 live bytes of the reference's 256-byte-strided record
+// (SURVEY §8 a1).  w == 1 and gid == index+1 are implicit; empty slots have a NaN position.
+struct SceneSoA {
+  float4 *pos_s0;    // x, y, z, log-scale.x
+  float4 *quat;      // w, x, y, z   (rot_0 = w, ipu_geometry.hpp:317)
+  float4 *rgba;      // r, g, b, opacity (raw)
+  float2 *s12;       // log-scale.y, log-scale.z
+  uint32_t n;
+};
+
+// K1 output per Gaussian, 48 B (only the slots of drawn Gaussians are written / read).
+struct Projected {
+  float4 *a;   // mean.x, mean.y, conic.x, conic.y
+  float4 *b;   // conic.z, opacity (0 when det == 0), r, g
+  float4 *c;   // b, clip z, rect {c0 | c1<<16}, rect {r0 | r1<<16}  (last two are uint bit patterns)
+  uint32_t *touched;   // tiles touched (0 = not drawn)
+};
+
+constexpr int K1_THREADS = 256;
+
+// ---- launchers (all asynchronous on `st`) ------------------------------------------------
+void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st);
+// K1: writes Projected + per-block sums of `touched` (block_sums[gridDim]).
+void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *block_sums,
+                    uint32_t *drawn_counter, float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st);
+// Debug/parity entry: fill c.{z,rect}/touched from caller-supplied projected inputs.
+void launch_inject(const float *depth, const int32_t *rect4, const uint8_t *drawn, uint32_t n,
+                   const FrameParams &fp, Projected out, uint32_t *block_sums, uint32_t *drawn_counter,
+                   cudaStream_t st);
+// exclusive scan of block_sums[nblocks] in place; totals[0] = D, totals[1] = V is NOT computed here.
+void launch_scan_block_sums(uint32_t *block_sums, uint32_t nblocks, uint32_t *total, cudaStream_t st);
+// K2: emits (tile<<32 | depth-key, gaussian index) in gid order; sets *overflow if D > capacity.
+void launch_duplicate(const Projected &p, uint32_t n, const uint32_t *block_offsets,
+                      int tiles_across, uint64_t *keys, uint32_t *vals, uint32_t capacity,
+                      uint32_t *overflow, cudaStream_t st);
+
+// K3: stable LSD radix sort of the low `key_bits` bits, 8-bit digits.  n is read on the device
+// from *d_n (clamped to capacity).  Result ends in keys_out/vals_out pointers returned.
+struct SortBuffers {
+  uint64_t *keys[2];
+  uint32_t *vals[2];
+  uint32_t *block_hist;   // 256 * max_blocks
+  uint32_t *digit_base;   // 256
+  uint32_t capacity;      // elements
+  uint32_t max_blocks;
+};
+constexpr int RS_THREADS = 256;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
+// returns index (0/1) of the buffer holding the sorted result
+int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int key_bits,
+                      cudaStream_t st);
+
+// K4: per-tile [start,end) over the sorted keys.
+void launch_tile_ranges(const uint64_t *keys, const uint32_t *d_n, uint32_t n_upper, uint32_t cap,
+                        uint2 *ranges, uint32_t num_tiles, cudaStream_t st);
+
+// K5: front-to-back blend of every tile of the band, writes the tile-major f32 framebuffer and
+// the per-tile counts.
+void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges,
+                  const FrameParams &fp, float4 *fb_tiled, uint32_t *counts, cudaStream_t st);
+
+// a10: tiled f32 RGBA -> de-tiled BGR8 rows.
+void launch_bgr8(const float4 *fb_tiled, uint8_t *bgr, int W, int H, int tile_w, int tile_h,
+                 cudaStream_t st);
+
+inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+}  // namespace gsplat

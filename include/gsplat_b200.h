@@ -1,0 +1,151 @@
+/* gsplat_b200.h — C ABI of libgsplat_b200.so, the B200 (sm_100a) Gaussian-splat render core.
+ *
+ * This library replaces ONE path of Nmjfry/gaussian_splat_ipu: the per-frame project -> route to
+ * tiles -> z-order -> alpha-blend work that the reference spreads over IPU tiles
+ * (codelets/splat/codelets.cpp:143-641 `GSplat`, include/tileMapping/tile_config.hpp,
+ * src/splat/ipu_rasteriser.cpp, src/splat/edge_builder.cpp).  The reference has no FFI layer; its
+ * boundary for this path is the C++ class `splat::IpuSplatter`
+ * (include/splat/ipu_rasteriser.hpp:20-55).  Each entry point below names the IpuSplatter member
+ * (or codelet field) it stands in for.  All paths are relative to the reference tree.
+ *
+ * Conventions
+ *   - plain C, no exceptions: every call returns GSPLAT_OK (0) or a negative gsplat_status;
+ *     gsplat_last_error() gives the message of the last failure on that context
+ *     (reference: std::runtime_error / poplar exceptions, include/ipu/ipu_utils.hpp:531-546).
+ *   - a context owns one CUDA device, one stream and all device / pinned memory; every pointer
+ *     argument is caller-owned and only touched during the call.
+ *   - calls on one context are not re-entrant; distinct contexts are independent (one per GPU /
+ *     view).  gsplat_render() is asynchronous on the context's stream; gsplat_read_*() and
+ *     gsplat_sync() wait for it.
+ *   - matrices are 16 floats in glm memory order (column-major, what glm::value_ptr yields).
+ *   - there is NO CPU fallback: without a CUDA device gsplat_create() fails with GSPLAT_E_CUDA.
+ */
+#ifndef GSPLAT_B200_H
+#define GSPLAT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSPLAT_ABI_VERSION 1
+
+typedef enum gsplat_status {
+  GSPLAT_OK = 0,
+  GSPLAT_E_ARG = -1,      /* bad argument / call order                                   */
+  GSPLAT_E_CUDA = -2,     /* CUDA runtime error (message has the cudaError string)       */
+  GSPLAT_E_CAPACITY = -3, /* duplicate buffer could not be grown (never a silent drop;   */
+                          /* the reference drops silently, codelets.cpp:565-569)         */
+  GSPLAT_E_STATE = -4     /* e.g. render before upload_scene / set_camera                */
+} gsplat_status;
+
+typedef struct gsplat_ctx gsplat_ctx;
+
+/* Geometry and constants of the path.  Defaults = the reference's compile-time values. */
+typedef struct gsplat_config {
+  int device;            /* CUDA ordinal                                                       */
+  int width, height;     /* image size; IMWIDTH/IMHEIGHT, tile_config.hpp:5-6 (1280x720)      */
+  int tile_w, tile_h;    /* semantic tile; IPU_TILEWIDTH/HEIGHT, tile_config.hpp:9-15 (32x20); */
+                         /* must divide width/height                                          */
+  float guard_factor;    /* clipSize, codelets.cpp:622 (15): bbox diagonal < 15 tile diagonals */
+  int band_row_begin;    /* tile-row band [begin,end) this context renders (multi-GPU tile    */
+  int band_row_end;      /* bands); 0,0 = all rows                                */
+  int collect_timings;   /* record per-stage cudaEvents (gsplat_get_timings)                  */
+  int debug_records;     /* K1 also writes the projected records for gsplat_read_projected    */
+  size_t dup_capacity;   /* initial capacity of the (tile,Gaussian) duplicate buffers;        */
+                         /* 0 = choose from the scene size; grows on demand                   */
+} gsplat_config;
+
+/* Fills *cfg with the reference defaults (1280x720, 32x20, guard 15, device 0). */
+int gsplat_config_default(gsplat_config *cfg);
+
+/* IpuSplatter::IpuSplatter + GraphManager::compileOrLoad/prepareEngine
+ * (ipu_rasteriser.cpp:49-83,250-406; ipu_utils.hpp:548-610): device setup, buffers. */
+int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out);
+void gsplat_destroy(gsplat_ctx *ctx);
+const char *gsplat_last_error(const gsplat_ctx *ctx); /* ctx may be NULL: last create() error */
+
+/* Scene upload == the "write_verts" program (ipu_rasteriser.cpp:59-68,401-405,409-418).
+ * `gaussians16` holds n records of the reference's Gaussian3D (ipu_geometry.hpp:305-311):
+ * mean(x,y,z,w) colour(r,g,b,opacity) rot(w,x,y,z) scale(3, log) gid.  Records are converted to
+ * the SoA layout on the device; gid <= 0 marks an empty slot (codelets.cpp:456), any gid > 0 is
+ * treated as index+1 (src/main/splat.cpp:161). */
+int gsplat_upload_scene(gsplat_ctx *ctx, const float *gaussians16, size_t n);
+
+/* updateModelView + updateProjection + updateFocalLengths (ipu_rasteriser.cpp:86-110): the
+ * per-frame inputs.  fov = fxy[0] (radians), scale_div = fxy[1] (src/main/splat.cpp:262). */
+int gsplat_set_camera(gsplat_ctx *ctx, const float modelview[16], const float projection[16],
+                      float fov, float scale_div);
+
+/* One run of the "project" program (ipu_rasteriser.cpp:393-399,408-420), converged
+ * (SURVEY §8a): K1 project/cull, K2 duplicate, K3 radix sort, K4 tile ranges, K5 blend. */
+int gsplat_render(gsplat_ctx *ctx);
+int gsplat_sync(gsplat_ctx *ctx);
+
+/* outputFramebuffer stream (ipu_rasteriser.cpp:280-285,398): width*height*4 floats, tile-major:
+ * tile t = row*tiles_across + col holds tile_w*tile_h RGBA pixels, row-major inside the tile. */
+int gsplat_read_framebuffer_tiled_f32(gsplat_ctx *ctx, float *dst);
+/* IpuSplatter::getFrameBuffer (ipu_rasteriser.cpp:115-144): min(v*255,255) -> u8 (round half
+ * even, clamp >= 0) -> RGBA2BGR -> de-tiled rows; dst is height rows of `pitch` bytes (>= 3*width).
+ * The conversion runs on the device; only the BGR8 image crosses PCIe. */
+int gsplat_read_framebuffer_bgr8(gsplat_ctx *ctx, uint8_t *dst, size_t pitch);
+/* counts stream / IpuSplatter::getIPUHistogram (ipu_rasteriser.cpp:104-106,321-324,399;
+ * codelets.cpp:501-504): Gaussians in each tile's render list, tiles_across*tiles_down values
+ * (tiles outside the band are 0). */
+int gsplat_read_tile_counts(gsplat_ctx *ctx, uint32_t *dst);
+
+typedef struct gsplat_frame_stats {
+  uint64_t num_gaussians; /* N                                             */
+  uint64_t num_drawn;     /* V: Gaussians passing the render predicate      */
+  uint64_t num_duplicates;/* D: sum of per-tile list lengths                */
+  uint64_t dup_capacity;  /* current capacity of the duplicate buffers      */
+  uint32_t max_tile_count;
+  uint32_t num_tiles;     /* tiles_across * tiles_down                      */
+  uint32_t regrown;       /* 1 if this frame had to be re-run after growing */
+  uint32_t key_bits;      /* key bits the radix sort covered                */
+} gsplat_frame_stats;
+int gsplat_get_frame_stats(gsplat_ctx *ctx, gsplat_frame_stats *out);
+
+/* Stage timings of the last frame in milliseconds (needs collect_timings):
+ * [0] K1 project  [1] offsets scan  [2] K2 duplicate  [3] K3 sort  [4] K4 ranges  [5] K5 blend
+ * [6] BGR8 post (last read_framebuffer_bgr8)  [7] whole frame.  Returns the count written. */
+#define GSPLAT_NUM_TIMINGS 8
+int gsplat_get_timings(gsplat_ctx *ctx, float *ms, int capacity);
+
+/* ---- parity / debug taps (the reference exposes no equivalent; they exist so the stages can be
+ * checked one by one against the oracle) ------------------------------------------------------ */
+/* Projected records of the last frame (needs debug_records): rec8 = n x {px, py, clip_z, cov_a,
+ * cov_b, cov_c, radius, drawn}; rect4 = n x {c0, c1, r0, r1} tile rectangle (valid iff drawn). */
+int gsplat_read_projected(gsplat_ctx *ctx, float *rec8, int32_t *rect4);
+/* Per-tile render lists of the last frame: offsets[num_tiles+1], lists[offsets[num_tiles]]
+ * (Gaussian index = gid-1, in blend order).  lists may be NULL to query sizes only. */
+int gsplat_read_tile_lists(gsplat_ctx *ctx, int64_t *offsets, int32_t *lists, size_t lists_capacity);
+/* Runs K2-K4 (and K5 when `blend` != 0) from caller-supplied projected inputs instead of K1's:
+ * depth[n] = clip z, rect4 as above, drawn[n] (0/1).  K5 then uses the records of the last
+ * gsplat_render().  "Per-tile lists bit-exact given identical projected inputs". */
+int gsplat_bin_projected(gsplat_ctx *ctx, const float *depth, const int32_t *rect4,
+                         const uint8_t *drawn, size_t n, int blend);
+/* Stand-alone run of the K3 device radix sort on caller data (key_bits low bits are sorted,
+ * stable): used by the sort known-answer tests. */
+int gsplat_sort_pairs(gsplat_ctx *ctx, uint64_t *keys, uint32_t *values, size_t n, int key_bits);
+
+/* ---- helpers ------------------------------------------------------------------------------- */
+/* Pinned host memory for frame read-back buffers (cudaHostAlloc / cudaFreeHost). */
+int gsplat_host_alloc(void **ptr, size_t bytes);
+int gsplat_host_free(void *ptr);
+/* Device pointer of the BGR8 image / tiled f32 framebuffer of this context (for NCCL gathers of
+ * bands / views by the caller's communicator; valid until destroy). */
+int gsplat_device_framebuffer(gsplat_ctx *ctx, void **bgr8, void **tiled_f32);
+/* Runs the BGR8 post-process on the device without copying to the host. */
+int gsplat_postprocess_bgr8(gsplat_ctx *ctx);
+/* Seeded synthetic scene of SURVEY §8d (xoshiro256**, Box-Muller), written as n Gaussian3D
+ * records with the app's recentre + z-negate applied (src/main/splat.cpp:93-100). */
+int gsplat_synth_scene(uint64_t seed, size_t n, float *gaussians16);
+int gsplat_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSPLAT_B200_H */
