@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""bench.py — frames/s and M Gaussians splatted/s of the splat hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W [--workload NAME] [--impl reference]
+
+A step renders ONE frame per GPU: rank r renders view (step*N + r) of a camera orbit around a
+replicated synthetic scene (multi-view sharding; no data-path collective), so the
+per-GPU work is fixed as N grows ("weak").  `value` is whole-job frames/s with the scene resident
+in HBM; `e2e` is the same metric through the reference-facing API with host buffers: camera
+matrices from host memory in, BGR8 frame + per-tile counts out to pinned host memory, every step.
+`--impl reference` times the reference's own CPU code for the path (oracle/_ref; the C port of it
+when that library is absent) on the host cores, same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from gaussian_splat_ipu_b200 import scene as sc  # noqa: E402
+
+WORKLOADS = {
+    # name: (N gaussians, W, H, seed, description)
+    "synthetic-6M-1080p": (6_000_000, 1920, 1080, 0xB2000006, "north-star target: 6M synthetic Gaussians at 1920x1080"),
+    "synthetic-1M-1080p": (1_000_000, 1920, 1080, 0xB2000003, "BASELINE configs[2]: 1M synthetic Gaussians at 1920x1080"),
+    "synthetic-6M-4k": (6_000_000, 3840, 2160, 0xB2000004, "BASELINE configs[3]: 6M synthetic Gaussians at 3840x2160"),
+    "synthetic-3M-1080p": (3_000_000, 1920, 1080, 0xB2000005, "BASELINE configs[4] scene: 3M synthetic Gaussians at 1920x1080"),
+    "synthetic-200k-720p": (200_000, 1280, 720, 0xB2000001, "small functional check"),
+}
+DEFAULT_WORKLOAD = "synthetic-6M-1080p"
+ORBIT_VIEWS = 64
+FOV = sc.DEFAULT_FOV
+SCALE_DIV = 1.0
+
+
+def make_scene(name):
+    from gaussian_splat_ipu_b200.splatter import synth_scene
+    n, W, H, seed, _ = WORKLOADS[name]
+    g = synth_scene(n, seed)
+    bb = sc.bounds(g[:, 0:3])
+    base = sc.look_at_bounding_box(bb, (0.0, 1.0, 1.0), 1.0)
+    proj = sc.app_projection(g, FOV, W, H)
+    return g, base, proj, W, H
+
+
+def view_for(base, k):
+    return sc.rotate(base, np.radians(np.float32(360.0 / ORBIT_VIEWS * (k % ORBIT_VIEWS))), (0.0, 1.0, 0.0))
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU during the timed region (NVML)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._stop_ev = index, [], set(), None, threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self._stop_ev.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            self._stop_ev.wait(0.05)
+
+    def finish(self):
+        self._stop_ev.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            return json.load(fh), "measured"
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+def cpu_frame_time(kind, g, view, proj, W, H, threads=0):
+    from oracle import pyoracle
+    orc = pyoracle.Oracle(kind)
+    t0 = time.perf_counter()
+    f = orc.frame(g, view, proj, FOV, SCALE_DIV, W, H, render=True, threads=threads)
+    return time.perf_counter() - t0, orc.cores, f
+
+
+def reference_arm(args):
+    """The reference's CPU implementation of the path on the host cores (rank 0 only)."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    from oracle import pyoracle
+    kind = "reference" if pyoracle.have_ref() else "port"
+    g, base, proj, W, H = make_scene(args.workload)
+    n = g.shape[0]
+    # bounded sample: one step = one frame of the same scene/camera orbit on ALL host threads
+    times = []
+    cores = 0
+    for k in range(args.warmup + args.steps):
+        dt, cores, _ = cpu_frame_time(kind, g, view_for(base, k), proj, W, H)
+        if k >= args.warmup:
+            times.append(dt)
+    total = float(np.sum(times))
+    fps = args.steps / total
+    line = {"impl": "reference", "metric": "frames_per_second", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "gaussians": n, "width": W, "height": H, "tile": "32x20",
+                       "scale_div": SCALE_DIV, "views": "orbit"},
+            "mgaussians_per_s": n * fps / 1e6,
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
+                             "sample": f"{args.steps} full frames of {args.workload}, all host threads (OpenMP)"},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def stage_rooflines(tm, st, pairs, blended, W, H, tiles, clocks_mhz, peaks):
+    """Per-stage achieved vs roofline from ALGORITHMIC bytes / flops."""
+    N, V, D = st.num_gaussians, st.num_drawn, st.num_duplicates
+    passes = (st.key_bits + 7) // 8
+    hbm = peaks["hbm_gbs"]
+    mhz = clocks_mhz or peaks.get("sm_max_mhz", 1965.0)
+    fp32_peak = 2 * 128 * 148 * mhz * 1e6 / 1e12          # TFLOP/s at the observed SM clock
+    alg_bytes = {"k1_project": 56 * N + 52 * V, "k2_duplicate": 4 * N + 16 * V + 12 * D,
+                 "k3_sort": (8 + 24) * passes * D, "k4_ranges": 8 * D + 8 * tiles}
+    out = {}
+    for k, b in alg_bytes.items():
+        ms = tm[k]
+        ach = b / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        out[k] = {"ms": ms, "bound": "hbm", "alg_bytes": int(b), "achieved": ach, "peak": hbm, "unit": "GB/s",
+                  "frac": ach / hbm}
+    flops = 14 * pairs + 13 * blended
+    ms = tm["k5_blend"]
+    ach = flops / (ms * 1e-3) / 1e12 if ms > 0 else 0.0
+    out["k5_blend"] = {"ms": ms, "bound": "fp32", "alg_flops": int(flops), "pairs": int(pairs), "blended": int(blended),
+                       "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
+                       "alg_bytes": int(52 * D + 16 * W * H), "sm_mhz": mhz}
+    return out
+
+
+def gpu_arm(args):
+    from gaussian_splat_ipu_b200.splatter import B200Splatter, PinnedBuffer, launch_count
+    rank, world, local = dist_env()
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    g, base, proj, W, H = make_scene(args.workload)
+    n = g.shape[0]
+    s = B200Splatter(g, W, H, device=local, collect_timings=True)
+    s.updateProjection(proj)
+    s.updateFocalLengths(FOV, SCALE_DIV)
+
+    def step(k):
+        s.updateModelView(view_for(base, k * world + rank))
+        s.execute()
+
+    K, Wm = args.steps, args.warmup
+    for k in range(Wm):
+        step(k)
+    s.sync()
+    s.timings_accum(reset=True)
+
+    # ---- device-resident leg: scene in HBM, K frames back to back -----------------------------
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    l0 = launch_count()
+    t0 = time.perf_counter()
+    s.timer_begin()
+    for k in range(K):
+        step(Wm + k)
+    dev_ms = s.timer_end()          # waits for the last frame
+    wall = time.perf_counter() - t0
+    launches = launch_count() - l0
+    barrier()
+    clocks = sampler.finish()
+    tm, nframes = s.timings_accum(reset=True)
+    st = s.stats()
+    t_max = max_over_ranks(wall)
+    dev_ms_max = max_over_ranks(dev_ms)
+    fps = world * K / t_max
+
+    # ---- end-to-end leg: host camera in, BGR8 frame + tile counts out to pinned host memory ---
+    frame = PinnedBuffer((H, W, 3), np.uint8)
+    for k in range(2):
+        step(k); s.getFrameBuffer(frame.array); s.getIPUHistogram()
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(K):
+        step(Wm + k)
+        s.getFrameBuffer(frame.array)
+        counts = s.getIPUHistogram()
+    e2e_wall = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e_fps = world * K / e2e_wall
+    checksum = int(frame.array[::7, ::7].astype(np.uint64).sum()) + int(counts.sum())
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    # ---- accounting on rank 0 ------------------------------------------------------------------
+    peaks, peak_src = measured_peaks()
+    step(Wm)
+    s.sync()
+    pairs, blended = s.count_pairs()
+    st = s.stats()
+    stages = stage_rooflines(tm, st, pairs, blended, W, H, s.num_tiles, clocks["sm_mhz"], peaks)
+    dom = max(stages, key=lambda k: stages[k]["ms"])
+    r = stages[dom]
+    roofline = {"kernel": dom, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
+                "frac": r["frac"], "traffic": None, "peak_source": peak_src, "ms": r["ms"]}
+    cpu = None
+    if args.gpus == 1 and not args.no_cpu_baseline:
+        from oracle import pyoracle
+        kind = "reference" if pyoracle.have_ref() else "port"
+        dt, cores, _ = cpu_frame_time(kind, g, view_for(base, Wm), proj, W, H)
+        cpu = {"value": 1.0 / dt, "unit": "frames/s", "cores": cores, "kind": kind,
+               "sample": f"1 full frame of {args.workload} (view {Wm}), all host threads (OpenMP), {dt:.2f} s"}
+    line = {"metric": "frames_per_second", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": 1e3 * t_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "gaussians": n, "width": W, "height": H, "tile": "32x20",
+                       "scale_div": SCALE_DIV, "views": f"orbit of {ORBIT_VIEWS}, one view per GPU per step",
+                       "l2": "inputs larger than L2 (scene + records > 126 MB) and a new camera every step"},
+            "mgaussians_per_s": n * fps / 1e6, "device_ms_per_step": dev_ms_max / K,
+            "frame": {"drawn": int(st.num_drawn), "duplicates": int(st.num_duplicates),
+                      "max_tile_count": int(st.max_tile_count), "pairs": pairs, "blended": blended},
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": 34 * 4,
+                    "d2h_bytes_per_step": W * H * 3 + s.num_tiles * 8 + 8, "checksum": checksum},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "stages": stages,
+            "cpu_baseline": cpu}
+    if args.stage_report:
+        with open(args.stage_report, "w") as fh:
+            json.dump(line, fh, indent=1)
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--stage-report", default=None, help="write the per-stage roofline table (JSON) to this path")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -11,26 +11,50 @@
 // There is no per-pixel bbox test in the reference: a Gaussian contributes to exactly the pixels
 // of the 32x20 tiles its rectangle covers, so the CTA *is* the semantic tile.
 //
-// Mapping: one CTA per tile, one warp per 32x4 pixel strip, 4 pixels (one column of the strip)
-// per thread held in registers; the list is staged through shared memory in batches of
-// blockDim.x records gathered by index (idx 4 B + record 36 B per duplicate, once per tile).
-// Stores to the tile-major framebuffer are 512 B contiguous per warp row.
+// Mapping: one CTA per tile, one warp per pixel ROW of the tile (32 px), one pixel per thread in
+// registers.  The list is staged through shared memory in batches of blockDim.x records gathered
+// by index; the staging thread also derives, per Gaussian, the rows of the tile on which
+// alpha >= 1/255 is possible at all (y-extent of the ellipse power >= ln(1/(255 opacity)),
+// conservative).  Each row-warp ballots over those row ranges and only walks the Gaussians that
+// can touch its row: skipped pairs are exactly pairs the reference loop `continue`s over, so the
+// result is unchanged while tiny splats cost ~nothing on the rows they miss.
+// exp() is ex2.approx.ftz on a log2e-prescaled conic.  FP32-pipe bound; no tensor cores (each
+// pair has its own quadratic form).  Stores are 512 B contiguous per warp.
 #include "gsplat_internal.h"
 
 namespace gsplat {
 
-constexpr int PX = 4;            // pixels per thread (rows of a strip)
-constexpr int BLEND_MAX_WARPS = 8;
+unsigned long long g_launches = 0;
 
-__global__ void __launch_bounds__(BLEND_MAX_WARPS * 32)
+constexpr int BLEND_MAX_ROWS = 32;
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float ALPHA_MIN = 1.0f / 255.0f;
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// Shared-memory batch, blockDim.x entries of each (dynamic, sized by the launcher):
+//   sA float4: mean.x, mean.y, -0.5*log2e*A, -log2e*B     sB float4: -0.5*log2e*C, opacity, r, g
+//   sC float2: b, conservative log2 threshold (skip when power2 < it)
+//   sRows u16: row_lo | row_hi << 8 ; lo > hi: touches no row
+constexpr size_t BLEND_SMEM_PER_THREAD = 16 + 16 + 8 + 2;
+
+template <bool COUNT>
+__global__ void __launch_bounds__(BLEND_MAX_ROWS * 32)
 blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
              int tiles_across, int row_begin, int tile_h, float4 *__restrict__ fb,
-             uint32_t *__restrict__ counts) {
-  __shared__ float4 sA[BLEND_MAX_WARPS * 32];   // mean.x, mean.y, conic.x, conic.y
-  __shared__ float4 sB[BLEND_MAX_WARPS * 32];   // conic.z, opacity, r, g
-  __shared__ float sC[BLEND_MAX_WARPS * 32];    // b
-  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+             uint32_t *__restrict__ counts, unsigned long long *__restrict__ pair_counters) {
+  extern __shared__ __align__(16) unsigned char blend_smem_raw[];
+  const long long t_begin = COUNT ? clock64() : 0;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, row = tid >> 5;
   const uint32_t nthreads = blockDim.x;
+  float4 *sA = reinterpret_cast<float4 *>(blend_smem_raw);
+  float4 *sB = sA + nthreads;
+  float2 *sC = reinterpret_cast<float2 *>(sB + nthreads);
+  uint16_t *sRows = reinterpret_cast<uint16_t *>(sC + nthreads);
   const uint32_t tile = blockIdx.x + (uint32_t)row_begin * tiles_across;
   const uint2 range = ranges[tile];
   const uint32_t n = range.y - range.x;
@@ -38,77 +62,125 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
 
   const uint32_t tcol = tile % tiles_across, trow = tile / tiles_across;
   const float xf = (float)(tcol * 32 + lane);
-  const float y0 = (float)(trow * tile_h + warp * PX);
+  const float ty0 = (float)(trow * tile_h);
+  const float yf = ty0 + (float)row;
 
-  float T[PX], Cr[PX], Cg[PX], Cb[PX], Ca[PX];
-#pragma unroll
-  for (int k = 0; k < PX; ++k) { T[k] = 1.f; Cr[k] = Cg[k] = Cb[k] = Ca[k] = 0.f; }
-  uint32_t live = (1u << PX) - 1;   // bit k: pixel k has not hit the transmittance stop
+  float T = 1.f, Cr = 0.f, Cg = 0.f, Cb = 0.f, Ca = 0.f;
+  bool done = false;
+  uint32_t stop_at = n;            // COUNT: list entries this pixel visits (reference semantics)
+  unsigned long long n_blend = 0;  // COUNT
 
   for (uint32_t base = 0; base < n; base += nthreads) {
+    // ---- stage one batch: gather the record, prescale, derive the row range ----------------
     const uint32_t j = base + tid;
     if (j < n) {
       const uint32_t g = vals[range.x + j];
-      sA[tid] = __ldg(&p.a[g]);
-      sB[tid] = __ldg(&p.b[g]);
-      sC[tid] = __ldg(&p.c[g].x);
+      const float4 a = __ldg(&p.a[g]);
+      const float4 b = __ldg(&p.b[g]);
+      const float cb = __ldg(&p.c[g].x);
+      const float A = a.z, B = a.w, C = b.x, op = b.y;
+      uint32_t lo = 1, hi = 0;
+      float thr2 = __int_as_float(0x7f800000);   // +inf: never passes
+      if (op * 255.0f > 1.0f) {                  // otherwise alpha = op*exp(<=0) < 1/255 everywhere
+        const float L2 = __log2f(op * 255.0f);   // power2 >= -L2  <=>  alpha >= 1/255
+        thr2 = -L2 - 0.02f;
+        lo = 0; hi = (uint32_t)tile_h - 1;
+        const float det = A * C - B * B;
+        if (det > 0.f && A > 0.f) {
+          // ellipse d^T Q d <= 2 ln(255 op): half-height sqrt(2L * A / det); padded
+          const float hy = sqrtf(2.0f * 0.6931472f * L2 * A / det) * 1.001f + 0.02f;
+          const float flo = ceilf(a.y - hy - ty0), fhi = floorf(a.y + hy - ty0);
+          if (fhi < 0.f || flo > (float)(tile_h - 1)) { lo = 1; hi = 0; }
+          else { lo = flo > 0.f ? (uint32_t)flo : 0u; hi = fhi < (float)(tile_h - 1) ? (uint32_t)fhi : (uint32_t)tile_h - 1; }
+        }
+      }
+      sA[tid] = make_float4(a.x, a.y, -0.5f * LOG2E * A, -LOG2E * B);
+      sB[tid] = make_float4(-0.5f * LOG2E * C, op, b.z, b.w);
+      sC[tid] = make_float2(cb, thr2);
+      sRows[tid] = (uint16_t)(lo | (hi << 8));
     }
     __syncthreads();
     const uint32_t m = min(nthreads, n - base);
-    if (live) {
-      for (uint32_t jj = 0; jj < m; ++jj) {
-        const float4 a = sA[jj];
-        const float4 b = sB[jj];
-        const float dx = a.x - xf;
-        const float hx = -0.5f * a.z * dx * dx;   // -0.5 A dx^2
-        const float bx = -a.w * dx;               // -B dx
-        const float hc = -0.5f * b.x;             // -0.5 C
-        bool any = false;
-        float alpha[PX];
-#pragma unroll
-        for (int k = 0; k < PX; ++k) {
-          const float dy = a.y - (y0 + (float)k);
-          const float power = hx + dy * (bx + hc * dy);
-          float al = fminf(0.99f, b.y * __expf(power));
-          if (power > 0.f || al < (1.0f / 255.0f) || !((live >> k) & 1u)) al = 0.f;
-          alpha[k] = al;
-          any |= al > 0.f;
-        }
-        if (any) {
-          const float cb = sC[jj];
-#pragma unroll
-          for (int k = 0; k < PX; ++k) {
-            if (alpha[k] > 0.f) {
-              const float test_T = T[k] * (1.f - alpha[k]);
+    if (!__all_sync(0xffffffffu, done)) {
+      for (uint32_t c0 = 0; c0 < m; c0 += 32) {
+        const uint32_t jj = c0 + lane;
+        uint32_t rr = jj < m ? sRows[jj] : 1u;   // 1 = lo 1, hi 0: empty
+        uint32_t mask = __ballot_sync(0xffffffffu, row >= (rr & 0xffu) && row <= (rr >> 8));
+        while (mask) {
+          const uint32_t k = c0 + __ffs(mask) - 1;
+          mask &= mask - 1;
+          const float4 a = sA[k];
+          const float4 b = sB[k];
+          const float2 c = sC[k];
+          const float dx = a.x - xf, dy = a.y - yf;
+          // power * log2e = dx*(hA*dx + nB*dy) + hC*dy*dy
+          const float power2 = fmaf(b.x * dy, dy, dx * fmaf(a.w, dy, a.z * dx));
+          if (power2 <= 0.f && power2 >= c.y && !done) {
+            const float alpha = fminf(0.99f, b.y * ex2_approx(power2));
+            if (alpha >= ALPHA_MIN) {
+              const float test_T = T * (1.f - alpha);
               if (test_T < 0.0001f) {
-                live &= ~(1u << k);
+                done = true;
+                if (COUNT) stop_at = base + k + 1;
               } else {
-                const float w = alpha[k] * T[k];
-                Cr[k] += b.z * w; Cg[k] += b.w * w; Cb[k] += cb * w; Ca[k] += b.y * w;
-                T[k] = test_T;
+                const float w = alpha * T;
+                Cr = fmaf(b.z, w, Cr); Cg = fmaf(b.w, w, Cg); Cb = fmaf(c.x, w, Cb); Ca = fmaf(b.y, w, Ca);
+                T = test_T;
+                if (COUNT) ++n_blend;
               }
             }
           }
-          if (!live) break;
         }
+        if (__all_sync(0xffffffffu, done)) break;
       }
     }
     // all pixels of the tile stopped -> the rest of the list cannot contribute
-    if (__syncthreads_and(live == 0)) break;
+    if (__syncthreads_and(done)) break;
   }
 
-  float4 *dst = fb + (size_t)tile * (32 * tile_h) + (warp * PX) * 32 + lane;
+  if (COUNT) {
+    unsigned long long n_visit = stop_at;
 #pragma unroll
-  for (int k = 0; k < PX; ++k) dst[k * 32] = make_float4(Cr[k], Cg[k], Cb[k], Ca[k]);
+    for (int o = 16; o > 0; o >>= 1) {
+      n_visit += __shfl_xor_sync(0xffffffffu, n_visit, o);
+      n_blend += __shfl_xor_sync(0xffffffffu, n_blend, o);
+    }
+    if (lane == 0) {
+      atomicAdd(&pair_counters[0], n_visit); atomicAdd(&pair_counters[1], n_blend);
+      atomicAdd(&pair_counters[2 + 2 * (size_t)tile + 1], n_visit);            // per-tile profile tap
+      atomicMax(&pair_counters[2 + 2 * (size_t)tile], (unsigned long long)(clock64() - t_begin));
+    }
+  }
+  fb[(size_t)tile * (32 * tile_h) + tid] = make_float4(Cr, Cg, Cb, Ca);
+}
+
+template <bool COUNT>
+static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
+                           float4 *fb_tiled, uint32_t *counts, unsigned long long *pair_counters, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(blend_kernel<COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)(BLEND_MAX_ROWS * 32 * BLEND_SMEM_PER_THREAD));
+    attr_set = true;
+  }
+  const int rows = fp.row_end - fp.row_begin;
+  if (rows <= 0) return;
+  const int tile_h = (int)fp.tile_h;
+  // dynamic smem sized for this tile height so that 3 CTAs of a 32x20 tile fit per SM
+  const size_t smem = (size_t)tile_h * 32 * BLEND_SMEM_PER_THREAD;
+  ++g_launches;
+  blend_kernel<COUNT><<<rows * fp.tiles_across, tile_h * 32, smem, st>>>(
+      p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, tile_h, fb_tiled, counts, pair_counters);
 }
 
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
                   float4 *fb_tiled, uint32_t *counts, cudaStream_t st) {
-  const int rows = fp.row_end - fp.row_begin;
-  if (rows <= 0) return;
-  const int tile_h = (int)fp.tile_h;
-  blend_kernel<<<rows * fp.tiles_across, (tile_h / PX) * 32, 0, st>>>(p, sorted_vals, ranges, fp.tiles_across,
-                                                                     fp.row_begin, tile_h, fb_tiled, counts);
+  launch_blend_t<false>(p, sorted_vals, ranges, fp, fb_tiled, counts, nullptr, st);
+}
+
+void launch_blend_count(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
+                        float4 *fb_tiled, uint32_t *counts, unsigned long long *pair_counters, cudaStream_t st) {
+  launch_blend_t<true>(p, sorted_vals, ranges, fp, fb_tiled, counts, pair_counters, st);
 }
 
 // ---- a10: IpuSplatter::getFrameBuffer, src/splat/ipu_rasteriser.cpp:115-144 -----------------
@@ -145,6 +217,7 @@ bgr8_kernel(const float4 *__restrict__ fb, uint8_t *__restrict__ bgr, int W, int
 
 void launch_bgr8(const float4 *fb_tiled, uint8_t *bgr, int W, int H, int tile_w, int tile_h, cudaStream_t st) {
   const int quads = (W / 4) * H;
+  ++g_launches;
   bgr8_kernel<<<ceil_div(quads, 256), 256, 0, st>>>(fb_tiled, bgr, W, H, tile_w, tile_h, W / tile_w);
 }
 

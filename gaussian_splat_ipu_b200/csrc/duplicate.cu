@@ -61,6 +61,7 @@ scan_block_sums_kernel(uint32_t *__restrict__ sums, uint32_t nblocks, uint32_t *
 }
 
 void launch_scan_block_sums(uint32_t *block_sums, uint32_t nblocks, uint32_t *total, cudaStream_t st) {
+  ++g_launches;
   scan_block_sums_kernel<<<1, SCAN_THREADS, 0, st>>>(block_sums, nblocks, total);
 }
 
@@ -122,6 +123,7 @@ duplicate_kernel(Projected p, uint32_t n, const uint32_t *__restrict__ block_off
 void launch_duplicate(const Projected &p, uint32_t n, const uint32_t *block_offsets, int tiles_across,
                       uint64_t *keys, uint32_t *vals, uint32_t capacity, uint32_t *overflow, cudaStream_t st) {
   if (!n) return;
+  ++g_launches;
   duplicate_kernel<<<ceil_div(n, K1_THREADS), K1_THREADS, 0, st>>>(p, n, block_offsets, tiles_across, keys, vals,
                                                                   capacity, overflow);
 }

@@ -16,7 +16,7 @@ using namespace gsplat;
 namespace {
 thread_local std::string g_create_error;
 
-enum Ev { EV_START = 0, EV_K1, EV_SCAN, EV_K2, EV_K3, EV_K4, EV_K5, EV_POST0, EV_POST1, EV_COUNT };
+enum Ev { EV_START = 0, EV_K1, EV_SCAN, EV_K2, EV_K3, EV_K4, EV_K5, EV_POST0, EV_POST1, EV_T0, EV_T1, EV_COUNT };
 }  // namespace
 
 struct gsplat_ctx {
@@ -46,8 +46,14 @@ struct gsplat_ctx {
   FrameParams fp{};
   bool have_scene = false, have_camera = false, have_frame = false;
   gsplat_frame_stats stats{};
-  cudaEvent_t ev[EV_COUNT]{};
-  bool post_timed = false;
+  // stage events are double-buffered by frame parity so that a frame's timings can be folded
+  // into the accumulators at the NEXT frame's mid-frame sync without an extra wait
+  cudaEvent_t ev[2][EV_COUNT]{};
+  int cur_set = 0;
+  bool pending[2] = {false, false}, post_rec[2] = {false, false};
+  float last_ms[GSPLAT_NUM_TIMINGS] = {0};
+  double acc_ms[GSPLAT_NUM_TIMINGS] = {0};
+  uint64_t acc_frames = 0;
   int key_bits = 0;
 };
 
@@ -127,7 +133,7 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   free_sort(ctx->sort);
   dfree(ctx->ranges); dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
   if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
-  for (auto &e : ctx->ev) if (e) cudaEventDestroy(e);
+  for (auto &set : ctx->ev) for (auto &e : set) if (e) cudaEventDestroy(e);
   if (ctx->st) cudaStreamDestroy(ctx->st);
   delete ctx;
 }
@@ -171,7 +177,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   } while (0)
   CUC(cudaSetDevice(cfg->device));
   CUC(cudaStreamCreateWithFlags(&ctx->st, cudaStreamNonBlocking));
-  for (auto &ev : ctx->ev) CUC(cudaEventCreate(&ev));
+  for (auto &set : ctx->ev) for (auto &ev : set) CUC(cudaEventCreate(&ev));
   CUC(cudaMalloc(&ctx->d_scalars, 16 * sizeof(uint32_t)));
   CUC(cudaMemset(ctx->d_scalars, 0, 16 * sizeof(uint32_t)));
   CUC(cudaHostAlloc(&ctx->h_scalars, 16 * sizeof(uint32_t), cudaHostAllocDefault));

@@ -82,11 +82,16 @@ void launch_tile_ranges(const uint64_t *keys, const uint32_t *d_n, uint32_t n_up
 // the per-tile counts.
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges,
                   const FrameParams &fp, float4 *fb_tiled, uint32_t *counts, cudaStream_t st);
+// counting variant (roofline accounting): pair_counters[0] += visited pairs, [1] += blended pairs
+void launch_blend_count(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges,
+                        const FrameParams &fp, float4 *fb_tiled, uint32_t *counts,
+                        unsigned long long *pair_counters, cudaStream_t st);
 
 // a10: tiled f32 RGBA -> de-tiled BGR8 rows.
 void launch_bgr8(const float4 *fb_tiled, uint8_t *bgr, int W, int H, int tile_w, int tile_h,
                  cudaStream_t st);
 
+extern unsigned long long g_launches;   // kernels launched by this library (bench accounting)
 inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 }  // namespace gsplat

@@ -241,12 +241,14 @@ __global__ void aos_to_soa_kernel(const float4 *__restrict__ aos, SceneSoA s) {
 
 void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st) {
   if (!scene.n) return;
+  ++g_launches;
   aos_to_soa_kernel<<<ceil_div(scene.n, 256), 256, 0, st>>>(reinterpret_cast<const float4 *>(aos16), scene);
 }
 
 void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *block_sums,
                     uint32_t *drawn_counter, float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st) {
   if (!scene.n) return;
+  ++g_launches;
   project_kernel<<<ceil_div(scene.n, K1_THREADS), K1_THREADS, 0, st>>>(scene, fp, out, block_sums, drawn_counter,
                                                                       dbg_rec8, dbg_rect4);
 }
@@ -255,6 +257,7 @@ void launch_inject(const float *depth, const int32_t *rect4, const uint8_t *draw
                    const FrameParams &fp, Projected out, uint32_t *block_sums, uint32_t *drawn_counter,
                    cudaStream_t st) {
   if (!n) return;
+  ++g_launches;
   inject_kernel<<<ceil_div(n, K1_THREADS), K1_THREADS, 0, st>>>(depth, rect4, drawn, n, fp, out, block_sums,
                                                                drawn_counter);
 }

@@ -237,8 +237,11 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
   const int passes = (key_bits + 7) / 8;
   for (int p = 0; p < passes; ++p) {
     const int shift = p * 8;
+    ++g_launches;
     rs_hist_kernel<<<nb, RS_THREADS, 0, st>>>(sb.keys[cur], d_n, sb.capacity, shift, sb.block_hist, sb.max_blocks);
+    ++g_launches;
     rs_scan_kernel<<<256, 256, 0, st>>>(sb.block_hist, sb.max_blocks, d_n, sb.capacity, sb.digit_base);
+    ++g_launches;
     rs_scatter_kernel<<<nb, RS_THREADS, sizeof(RsSmem), st>>>(sb.keys[cur], sb.vals[cur], sb.keys[cur ^ 1],
                                                               sb.vals[cur ^ 1], d_n, sb.capacity, shift,
                                                               sb.block_hist, sb.max_blocks, sb.digit_base);
@@ -265,6 +268,7 @@ void launch_tile_ranges(const uint64_t *keys, const uint32_t *d_n, uint32_t n_up
   cudaMemsetAsync(ranges, 0, sizeof(uint2) * num_tiles, st);
   if (!n_upper) return;
   const int blocks = min(ceil_div(n_upper, 256), 148 * 8);
+  ++g_launches;
   tile_ranges_kernel<<<blocks, 256, 0, st>>>(keys, d_n, cap, ranges, num_tiles);
 }
 

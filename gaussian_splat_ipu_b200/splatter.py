@@ -67,6 +67,12 @@ SYMBOLS = {
     "gsplat_device_framebuffer": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
     "gsplat_postprocess_bgr8": (C.c_int, [_vp]),
     "gsplat_synth_scene": (C.c_int, [C.c_uint64, C.c_size_t, _fp]),
+    "gsplat_profile_tiles": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), _vp, _vp]),
+    "gsplat_get_timings_accum": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
+    "gsplat_timer_begin": (C.c_int, [_vp]),
+    "gsplat_timer_end": (C.c_int, [_vp, _fp]),
+    "gsplat_launch_count": (C.c_uint64, []),
+    "gsplat_count_pairs": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
 }
 
 _lib = None
@@ -98,6 +104,10 @@ def load_library():
             fn.restype, fn.argtypes = res, args
         _lib = lib
     return _lib
+
+
+def launch_count() -> int:
+    return int(load_library().gsplat_launch_count())
 
 
 def synth_scene(n: int, seed: int) -> np.ndarray:
@@ -267,6 +277,35 @@ class B200Splatter:
         b, f = _vp(), _vp()
         self._check(self.lib.gsplat_device_framebuffer(self.h, C.byref(b), C.byref(f)))
         return b.value, f.value
+
+    def timings_accum(self, reset=False):
+        """(mean ms per stage over the frames since the last reset, frame count)."""
+        ms = (C.c_double * NUM_TIMINGS)()
+        n = C.c_uint64()
+        self._check(self.lib.gsplat_get_timings_accum(self.h, ms, C.byref(n), int(reset)))
+        k = max(int(n.value), 1)
+        return dict(zip(TIMING_NAMES, [float(v) / k for v in ms])), int(n.value)
+
+    def timer_begin(self):
+        self._check(self.lib.gsplat_timer_begin(self.h))
+
+    def timer_end(self) -> float:
+        ms = C.c_float()
+        self._check(self.lib.gsplat_timer_end(self.h, C.byref(ms)))
+        return float(ms.value)
+
+    def count_pairs(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.gsplat_count_pairs(self.h, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
+
+    def profile_tiles(self):
+        """(pairs, blended, per-tile SM cycles, per-tile visited pairs) of a counting K5 re-run."""
+        a, b = C.c_uint64(), C.c_uint64()
+        cyc = np.zeros(self.num_tiles, np.uint64)
+        prs = np.zeros(self.num_tiles, np.uint64)
+        self._check(self.lib.gsplat_profile_tiles(self.h, C.byref(a), C.byref(b), cyc.ctypes.data, prs.ctypes.data))
+        return int(a.value), int(b.value), cyc, prs
 
     def postprocess_bgr8(self):
         self._check(self.lib.gsplat_postprocess_bgr8(self.h))

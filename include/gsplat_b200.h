@@ -113,6 +113,9 @@ int gsplat_get_frame_stats(gsplat_ctx *ctx, gsplat_frame_stats *out);
  * [6] BGR8 post (last read_framebuffer_bgr8)  [7] whole frame.  Returns the count written. */
 #define GSPLAT_NUM_TIMINGS 8
 int gsplat_get_timings(gsplat_ctx *ctx, float *ms, int capacity);
+/* Sums of the same GSPLAT_NUM_TIMINGS stage timings over all frames rendered since the last reset
+ * (folded in without extra synchronisation while frames are being rendered), and the frame count. */
+int gsplat_get_timings_accum(gsplat_ctx *ctx, double *ms_sum, uint64_t *frames, int reset);
 
 /* ---- parity / debug taps (the reference exposes no equivalent; they exist so the stages can be
  * checked one by one against the oracle) ------------------------------------------------------ */
@@ -127,8 +130,8 @@ int gsplat_read_tile_lists(gsplat_ctx *ctx, int64_t *offsets, int32_t *lists, si
  * gsplat_render().  "Per-tile lists bit-exact given identical projected inputs". */
 int gsplat_bin_projected(gsplat_ctx *ctx, const float *depth, const int32_t *rect4,
                          const uint8_t *drawn, size_t n, int blend);
-/* Stand-alone run of the K3 device radix sort on caller data (key_bits low bits are sorted,
- * stable): used by the sort known-answer tests. */
+/* Stand-alone run of the K3 device radix sort on caller data: stable sort on the low key_bits
+ * bits, rounded UP to whole 8-bit digits (17 -> 24).  Used by the sort known-answer tests. */
 int gsplat_sort_pairs(gsplat_ctx *ctx, uint64_t *keys, uint32_t *values, size_t n, int key_bits);
 
 /* ---- helpers ------------------------------------------------------------------------------- */
@@ -144,6 +147,22 @@ int gsplat_postprocess_bgr8(gsplat_ctx *ctx);
  * records with the app's recentre + z-negate applied (src/main/splat.cpp:93-100). */
 int gsplat_synth_scene(uint64_t seed, size_t n, float *gaussians16);
 int gsplat_abi_version(void);
+/* Device-time stopwatch on the context's stream (cudaEvent pair) for callers that time several
+ * frames: begin records an event now, end records another, waits for it and returns the
+ * milliseconds between them. */
+int gsplat_timer_begin(gsplat_ctx *ctx);
+int gsplat_timer_end(gsplat_ctx *ctx, float *ms);
+/* Kernel launches issued by this library since load (all contexts); for bench accounting. */
+uint64_t gsplat_launch_count(void);
+/* Re-runs K5 on the last frame's lists in counting mode: *pairs = number of (pixel, Gaussian)
+ * pairs the blend loop visits (list entries per pixel up to and including the one that trips the
+ * test_T < 1e-4 stop, codelets.cpp:405-408) — the unit the blend roofline is quoted in;
+ * *blended = pairs that passed the alpha test and were accumulated. */
+int gsplat_count_pairs(gsplat_ctx *ctx, uint64_t *pairs, uint64_t *blended);
+/* Same counting run, plus per tile (num_tiles entries each, may be NULL): SM cycles the tile's CTA
+ * took and the pairs it visited — the load-imbalance picture (reference README.md:16-17). */
+int gsplat_profile_tiles(gsplat_ctx *ctx, uint64_t *pairs, uint64_t *blended, uint64_t *tile_cycles,
+                         uint64_t *tile_pairs);
 
 #ifdef __cplusplus
 }
