@@ -80,6 +80,12 @@ class Oracle:
         f("num_threads", C.c_int, [])
         f("conic_opacity", None, [_fp, C.c_float, _fp])
         f("tile_bounds", None, [C.c_int] * 4 + [C.c_uint, _fp])
+        if kind == "reference":   # O1: the unmodified GSplat::compute over the 4-neighbour lattice
+            f("lattice_create", C.c_void_p, [_fp, C.c_size_t] + [C.c_int] * 4 + [C.c_size_t] * 2)
+            f("lattice_step", None, [C.c_void_p, _fp, _fp, C.c_float, C.c_float, C.c_int])
+            f("lattice_get", None, [C.c_void_p, C.POINTER(C.c_uint32), _fp, C.POINTER(C.c_double)])
+            f("lattice_rendered", C.c_size_t, [C.c_void_p, C.c_int, _fp, C.c_size_t])
+            f("lattice_destroy", None, [C.c_void_p])
         if kind == "port":
             f("frame_num_pairs", C.c_uint64, [C.c_void_p])
             f("framebuffer_to_bgr8", None, [_fp] + [C.c_int] * 4 + [C.POINTER(C.c_uint8)])
@@ -123,6 +129,36 @@ class Oracle:
         finally:
             self._frame_destroy(h)
         return Frame(rec, rect, counts, offsets, lists[:D], fb, tuple(ms), pairs)
+
+    def lattice(self, g16, view, proj, fov, scale_div, W, H, frames, spare_slots=600, chan_slots=75,
+                tile_w=32, tile_h=20, threads=0):
+        """O1 (kind="reference" only): run the reference's own GSplat vertices + edge lattice for
+        `frames` program runs (ipu_rasteriser.cpp:393-399); defaults = the as-shipped capacities
+        (ipu_rasteriser.cpp:307-316).  Returns (counts, fb_tiled, per-frame total counts,
+        per-tile rendered lists as (k,3) arrays of (mean.x, mean.y, z) in blend order)."""
+        assert self.kind == "reference"
+        g16 = np.ascontiguousarray(g16, dtype=np.float32).reshape(-1, 16)
+        view = np.ascontiguousarray(view, dtype=np.float32).ravel()
+        proj = np.ascontiguousarray(proj, dtype=np.float32).ravel()
+        TA, TD = W // tile_w, H // tile_h
+        h = self._lattice_create(g16.ctypes.data_as(_fp), g16.shape[0], W, H, TA, TD, spare_slots, chan_slots)
+        try:
+            counts = np.zeros(TA * TD, np.uint32)
+            fb = np.zeros(W * H * 4, np.float32)
+            ms = (C.c_double * 2)()
+            totals = []
+            for _ in range(frames):
+                self._lattice_step(h, view.ctypes.data_as(_fp), proj.ctypes.data_as(_fp), fov, scale_div, threads)
+                self._lattice_get(h, counts.ctypes.data_as(C.POINTER(C.c_uint32)), fb.ctypes.data_as(_fp), ms)
+                totals.append(int(counts.sum()))
+            held = []
+            buf = np.empty((g16.shape[0] + 1, 3), np.float32)
+            for t in range(TA * TD):
+                k = int(self._lattice_rendered(h, t, buf.ctypes.data_as(_fp), buf.shape[0])) if counts[t] else 0
+                held.append(buf[:k].copy())
+        finally:
+            self._lattice_destroy(h)
+        return counts, fb, totals, held
 
     def conic_opacity(self, cov, opacity):
         cov = np.ascontiguousarray(cov, np.float32)

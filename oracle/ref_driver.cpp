@@ -382,6 +382,20 @@ std::size_t ref_lattice_held(void *h, int t, int32_t *gids, std::size_t cap) {
   }
   return k;
 }
+// Rendered list of tile t after the last step: the first splatted[0] records of gaus2D (sorted
+// by renderTile's quicksort, codelets.cpp:360) as (mean.x, mean.y, z) triples.  Gaussian2D keeps
+// no gid (ipu_geometry.hpp:232-236), so the caller matches entries by these values.
+std::size_t ref_lattice_rendered(void *h, int t, float *xyz, std::size_t cap) {
+  auto *L = static_cast<Lattice *>(h);
+  const std::size_t S = sizeof(Gaussian2D);          // stride in FLOATS (codelets.cpp:370,494)
+  const std::size_t n = L->splatted[t][0];
+  for (std::size_t k = 0; k < n && k < cap; ++k) {
+    Gaussian2D g;
+    std::memcpy(&g, &L->gaus2D[t][k * S], sizeof(g));
+    xyz[k * 3 + 0] = g.mean.x; xyz[k * 3 + 1] = g.mean.y; xyz[k * 3 + 2] = g.z;
+  }
+  return n;
+}
 void ref_lattice_destroy(void *h) { delete static_cast<Lattice *>(h); }
 
 } // extern "C"
