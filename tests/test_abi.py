@@ -1,0 +1,109 @@
+"""CPU-only checks of the drop-in boundary: libgsplat_b200.so loads, exports every symbol that
+include/gsplat_b200.h declares, the ctypes mirror binds exactly that set, and — with no CUDA
+device — the product fails loudly instead of falling back to a CPU path."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from gaussian_splat_ipu_b200 import splatter as sp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "gsplat_b200.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gsplat_[a-z0-9_]+)\s*\(", src)))
+
+
+def have_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def test_library_exports_every_declared_symbol():
+    sp.build_library()
+    lib = C.CDLL(sp.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) >= 25
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in gsplat_b200.h but not exported"
+
+
+def test_ctypes_mirror_binds_the_declared_set():
+    assert sorted(sp.SYMBOLS) == declared_symbols()
+    lib = sp.load_library()
+    assert lib.gsplat_abi_version() == 1
+
+
+def test_config_defaults_are_the_reference_constants():
+    lib = sp.load_library()
+    cfg = sp.Config()
+    assert lib.gsplat_config_default(C.byref(cfg)) == 0
+    # tile_config.hpp:5-15 (1280x720, 40x36 tiles of 32x20), codelets.cpp:622 (clipSize 15)
+    assert (cfg.width, cfg.height, cfg.tile_w, cfg.tile_h) == (1280, 720, 32, 20)
+    assert cfg.guard_factor == 15.0 and cfg.device == 0
+    assert lib.gsplat_config_default(None) == -1
+
+
+def test_header_cites_the_reference_interface():
+    src = open(HEADER).read()
+    for cite in ("ipu_rasteriser.hpp:20-55", "ipu_rasteriser.cpp:86-110", "ipu_rasteriser.cpp:115-144",
+                 "codelets.cpp:143-641", "tile_config.hpp"):
+        assert cite in src
+
+
+def test_synth_scene_is_deterministic_and_in_spec():
+    """Host-only helper (SURVEY §8d generator): seeded, reproducible, reference record layout."""
+    a = sp.synth_scene(5000, 0xB2000003)
+    b = sp.synth_scene(5000, 0xB2000003)
+    c = sp.synth_scene(5000, 0xB2000004)
+    assert np.array_equal(a, b) and not np.array_equal(a, c)
+    assert a.shape == (5000, 16) and np.isfinite(a).all()
+    assert (a[:, 3] == 1.0).all()                                   # mean.w
+    assert np.array_equal(a[:, 15], np.arange(1, 5001, dtype=np.float32))   # gid = i+1
+    assert (a[:, 4:7] >= 0).all() and (a[:, 4:7] < 1).all()        # rgb ~ U[0,1)
+    assert (a[:, 7] >= 0.05).all() and (a[:, 7] < 1).all()         # opacity ~ U[0.05,1)
+    assert (a[:, 12:15] >= -13).all() and (a[:, 12:15] <= -0.5).all()
+    assert np.allclose(np.linalg.norm(a[:, 8:12], axis=1), 1.0, atol=1e-5)
+    # recentred on the bbox centroid (src/main/splat.cpp:93-100)
+    assert np.allclose(a[:, :3].max(0) + a[:, :3].min(0), 0, atol=1e-5)
+    # a prefix of a longer scene is the same stream
+    assert np.array_equal(sp.synth_scene(100, 7)[:, 4:15], sp.synth_scene(200, 7)[:100, 4:15])
+
+
+@pytest.mark.skipif(have_gpu(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback_without_a_device():
+    g = sp.synth_scene(10, 1)
+    with pytest.raises(sp.GsplatError) as e:
+        sp.B200Splatter(g, 1280, 720)
+    assert e.value.code == -2 and "no CPU fallback" in str(e.value)
+
+
+def test_argument_errors_do_not_need_a_device():
+    lib = sp.load_library()
+    cfg = sp.Config()
+    lib.gsplat_config_default(C.byref(cfg))
+    h = C.c_void_p()
+    cfg.width = 100                                   # 32 does not divide 100
+    assert lib.gsplat_create(C.byref(cfg), C.byref(h)) == -1 and not h.value
+    assert b"tile size" in lib.gsplat_last_error(None)
+    assert lib.gsplat_create(None, C.byref(h)) == -1
+    assert lib.gsplat_render(None) == -1 and lib.gsplat_sync(None) == -1
+
+
+def test_product_does_not_import_the_oracle():
+    """The oracle is test infrastructure: nothing under the package may import or load it."""
+    pkg = os.path.join(ROOT, "gaussian_splat_ipu_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cpp", ".h", ".hpp", ".inc", "Makefile")):
+                txt = open(os.path.join(dp, f), errors="replace").read()
+                assert "pyoracle" not in txt and "liboracle" not in txt and "splat_ref" not in txt, os.path.join(dp, f)
