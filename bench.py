@@ -153,12 +153,16 @@ def reference_arm(args):
 def stage_rooflines(tm, st, pairs, blended, W, H, tiles, clocks_mhz, peaks):
     """Per-stage achieved vs roofline from ALGORITHMIC bytes / flops."""
     N, V, D = st.num_gaussians, st.num_drawn, st.num_duplicates
-    passes = (st.key_bits + 7) // 8
+    tile_bits = st.key_bits - 32
+    pb = (tile_bits + 7) // 8                              # digits of sort B (sort A: 4 digits of 8 bits)
     hbm = peaks["hbm_gbs"]
     mhz = clocks_mhz or peaks.get("sm_max_mhz", 1965.0)
     fp32_peak = 2 * 128 * 148 * mhz * 1e6 / 1e12          # TFLOP/s at the observed SM clock
-    alg_bytes = {"k1_project": 56 * N + 52 * V, "k2_duplicate": 4 * N + 16 * V + 12 * D,
-                 "k3_sort": (8 + 24) * passes * D, "k4_ranges": 8 * D + 8 * tiles}
+    # per digit: 4 B histogram read + 8 B read + 8 B write per element (first digit of sort A
+    # generates its values: 4 B less)
+    alg_bytes = {"k1_project": 56 * N + 48 * V + 4 * N, "k3a_sort_depth": (4 * 20 - 4) * N,
+                 "k2_duplicate": 8 * N + 16 * V + 8 * D, "k3b_sort_tile": 20 * pb * D,
+                 "k4_ranges": 4 * D + 8 * tiles}
     out = {}
     for k, b in alg_bytes.items():
         ms = tm[k]
@@ -170,7 +174,7 @@ def stage_rooflines(tm, st, pairs, blended, W, H, tiles, clocks_mhz, peaks):
     ach = flops / (ms * 1e-3) / 1e12 if ms > 0 else 0.0
     out["k5_blend"] = {"ms": ms, "bound": "fp32", "alg_flops": int(flops), "pairs": int(pairs), "blended": int(blended),
                        "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
-                       "alg_bytes": int(52 * D + 16 * W * H), "sm_mhz": mhz}
+                       "alg_bytes": int((4 + 36) * D + 16 * W * H), "sm_mhz": mhz}
     return out
 
 

@@ -75,9 +75,10 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
     const uint32_t j = base + tid;
     if (j < n) {
       const uint32_t g = vals[range.x + j];
-      const float4 a = __ldg(&p.a[g]);
-      const float4 b = __ldg(&p.b[g]);
-      const float cb = __ldg(&p.c[g].x);
+      const float4 *r = p.rec + (size_t)g * 3;   // 48 contiguous bytes: two sectors of one line
+      const float4 a = __ldg(r);
+      const float4 b = __ldg(r + 1);
+      const float cb = __ldg(&r[2].x);
       const float A = a.z, B = a.w, C = b.x, op = b.y;
       uint32_t lo = 1, hi = 0;
       float thr2 = __int_as_float(0x7f800000);   // +inf: never passes

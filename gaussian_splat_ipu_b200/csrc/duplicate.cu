@@ -1,20 +1,22 @@
-// duplicate.cu — offsets scan + K2: tile-overlap duplication.
+// duplicate.cu — K2: tile-overlap duplication.
 //
 // Replaces the reference's whole exchange phase (send/protocol/readInput/insert over the
 // 4-neighbour lattice, codelets/splat/codelets.cpp:33-72,194-293,507-586 and
 // src/splat/edge_builder.cpp:35-84): every drawn Gaussian is emitted once per tile of its
-// converged rectangle as a 64-bit key (tile id << 32 | depth key) plus its index.
+// converged rectangle as a (tile id, Gaussian index) pair.
 //
-// Offsets come from a deterministic prefix sum over Gaussians in gid order (K1 leaves per-block
-// sums, one small kernel scans them, K2 re-derives the in-block prefix), so that the stable
-// radix sort that follows yields the canonical (z ascending, gid ascending) order per tile and
-// the lists are bit-reproducible — an unordered atomic cursor would not give that.
+// K2 walks the Gaussians in DEPTH order (the permutation sort A produced), so the emitted array is
+// globally ordered by (clip z, gid) and the stable sort by tile id that follows (sort B) leaves
+// every tile's list in the canonical (z ascending, gid ascending) order.  Offsets come from a
+// single-pass chained scan with decoupled look-back — deterministic prefix sums, not an unordered
+// atomic cursor — so the lists are bit-reproducible.  CTAs take their position in the chain from an
+// atomic ticket, which guarantees that every predecessor a CTA waits on is already running.
 #include "gsplat_internal.h"
 
 namespace gsplat {
 
 // Exclusive scan over 32-bit values for a block of THREADS threads; returns the exclusive prefix
-// and writes the block total to *total (all threads).
+// and the block total (all threads).
 template <int THREADS>
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *warp_tot /* THREADS/32+1 */,
                                                     uint32_t &total) {
@@ -44,88 +46,116 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *warp_t
   return r;
 }
 
-constexpr int SCAN_THREADS = 1024;
-__global__ void __launch_bounds__(SCAN_THREADS)
-scan_block_sums_kernel(uint32_t *__restrict__ sums, uint32_t nblocks, uint32_t *__restrict__ total) {
-  __shared__ uint32_t wt[SCAN_THREADS / 32 + 1];
-  uint32_t running = 0;
-  for (uint32_t base = 0; base < nblocks; base += SCAN_THREADS) {
-    const uint32_t i = base + threadIdx.x;
-    const uint32_t v = i < nblocks ? sums[i] : 0;
-    uint32_t tot;
-    const uint32_t ex = block_excl_scan<SCAN_THREADS>(v, wt, tot);
-    if (i < nblocks) sums[i] = running + ex;
-    running += tot;
-  }
-  if (threadIdx.x == 0) *total = running;
+// look-back word: flag in the top two bits, 62-bit value below (one 64-bit store publishes both)
+constexpr unsigned long long LB_AGGREGATE = 1ull << 62;   // value = this CTA's own total
+constexpr unsigned long long LB_PREFIX = 2ull << 62;      // value = inclusive prefix up to this CTA
+constexpr unsigned long long LB_VALUE = (1ull << 62) - 1;
+
+__device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-void launch_scan_block_sums(uint32_t *block_sums, uint32_t nblocks, uint32_t *total, cudaStream_t st) {
-  ++g_launches;
-  scan_block_sums_kernel<<<1, SCAN_THREADS, 0, st>>>(block_sums, nblocks, total);
-}
-
-// K2.  One CTA covers the same 256 Gaussians as the K1 CTA of the same index.  The CTA's
-// duplicates are a contiguous run [base, base + total) of the key array; the threads stride over
-// that run and find the owning Gaussian by binary search in the in-block prefix, so writes are
-// fully coalesced and a Gaussian covering hundreds of tiles does not serialise one thread.
-__global__ void __launch_bounds__(K1_THREADS)
-duplicate_kernel(Projected p, uint32_t n, const uint32_t *__restrict__ block_offsets, int tiles_across,
-                 uint64_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t capacity,
-                 uint32_t *__restrict__ overflow) {
-  __shared__ uint32_t wt[K1_THREADS / 32 + 1];
-  __shared__ uint32_t s_prefix[K1_THREADS + 1];
-  __shared__ uint32_t s_depth[K1_THREADS];
-  __shared__ uint32_t s_cols[K1_THREADS];   // c0 | width << 16
-  __shared__ uint32_t s_row0[K1_THREADS];
+__global__ void __launch_bounds__(K2_THREADS)
+duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const uint32_t *__restrict__ sorted_gauss,
+                 uint32_t n, int tiles_across, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals,
+                 uint32_t capacity, unsigned long long *__restrict__ lookback, uint32_t *__restrict__ ticket,
+                 uint32_t *__restrict__ total_out, uint32_t *__restrict__ overflow) {
+  __shared__ uint32_t wt[K2_THREADS / 32 + 1];
+  __shared__ uint32_t s_prefix[K2_THREADS + 1];
+  __shared__ uint32_t s_gauss[K2_THREADS];
+  __shared__ uint32_t s_cols[K2_THREADS];   // c0 | width << 16
+  __shared__ uint32_t s_row0[K2_THREADS];
+  __shared__ uint32_t s_chain;              // this CTA's position in the chain, then its base offset
   const uint32_t tid = threadIdx.x;
-  const uint32_t i = blockIdx.x * K1_THREADS + tid;
-  const uint32_t t = i < n ? p.touched[i] : 0;
+  if (tid == 0) s_chain = atomicAdd(ticket, 1u);
+  __syncthreads();
+  const uint32_t b = s_chain;
+  const uint32_t j = b * K2_THREADS + tid;   // position in depth order
+  uint32_t t = 0, g = 0, cols = 0, row0 = 0;
+  if (j < n && sorted_keys[j] != DEPTH_KEY_CULLED) {
+    g = sorted_gauss[j];
+    const float4 c = __ldg(&p.rec[(size_t)g * 3 + 2]);
+    const uint32_t cw = __float_as_uint(c.z), rw = __float_as_uint(c.w);
+    const uint32_t c0 = cw & 0xffffu, c1 = cw >> 16, r0 = rw & 0xffffu, r1 = rw >> 16;
+    cols = c0 | ((c1 - c0 + 1) << 16);
+    row0 = r0;
+    t = (c1 - c0 + 1) * (r1 - r0 + 1);
+  }
   uint32_t total;
-  const uint32_t ex = block_excl_scan<K1_THREADS>(t, wt, total);
-  if (total == 0) return;
-  const uint32_t base = block_offsets[blockIdx.x];
-  if (base + total > capacity || base + total < base) {   // never write past the buffer; host re-runs
-    if (tid == 0) atomicExch(overflow, 1u);
-    return;
+  const uint32_t ex = block_excl_scan<K2_THREADS>(t, wt, total);
+
+  // ---- chained scan: publish the aggregate, look back for the exclusive prefix ------------------
+  if (tid < 32) {
+    unsigned long long excl = 0;
+    if (b == 0) {
+      if (tid == 0) st_relaxed(&lookback[0], LB_PREFIX | total);
+    } else {
+      if (tid == 0) st_relaxed(&lookback[b], LB_AGGREGATE | total);
+      int pos = (int)b - 1;
+      while (true) {   // one warp inspects 32 predecessors at a time
+        const int q = pos - (int)tid;
+        unsigned long long w = LB_PREFIX;   // positions before the chain start count as prefix 0
+        if (q >= 0) {
+          do { w = ld_relaxed(&lookback[q]); } while ((w >> 62) == 0);
+        }
+        const uint32_t is_prefix = __ballot_sync(0xffffffffu, (w >> 62) == 2);
+        const int first = is_prefix ? __ffs(is_prefix) - 1 : 32;   // nearest predecessor with a full prefix
+        unsigned long long v = (int)tid <= first ? (w & LB_VALUE) : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        excl += v;
+        if (is_prefix) break;
+        pos -= 32;
+      }
+      if (tid == 0) st_relaxed(&lookback[b], LB_PREFIX | (excl + total));
+    }
+    if (tid == 0) {
+      const unsigned long long incl = excl + total;
+      if (b == gridDim.x - 1) *total_out = incl > 0xffffffffull ? 0xffffffffu : (uint32_t)incl;
+      if (incl > capacity) atomicExch(overflow, 1u);   // never write past the buffer; the host re-runs
+      s_chain = incl > capacity ? 0xffffffffu : (uint32_t)excl;
+    }
   }
   s_prefix[tid] = ex;
-  if (tid == 0) s_prefix[K1_THREADS] = total;
-  if (t) {
-    const float4 c = p.c[i];
-    const uint32_t cols = __float_as_uint(c.z), rows = __float_as_uint(c.w);
-    const uint32_t c0 = cols & 0xffffu, c1 = cols >> 16;
-    // depth key: drawn Gaussians have clip z < 0 (codelets.cpp:493); ascending z (:314) ==
-    // descending magnitude == ascending ~bits(z)
-    s_depth[tid] = ~__float_as_uint(c.y);
-    s_cols[tid] = c0 | ((c1 - c0 + 1) << 16);
-    s_row0[tid] = rows & 0xffffu;
-  }
+  if (tid == 0) s_prefix[K2_THREADS] = total;
+  s_gauss[tid] = g; s_cols[tid] = cols; s_row0[tid] = row0;
   __syncthreads();
-  for (uint32_t j = tid; j < total; j += K1_THREADS) {
-    // largest g with s_prefix[g] <= j  (zero-count entries share their successor's prefix and are skipped)
-    uint32_t lo = 0, hi = K1_THREADS;
+  const uint32_t base = s_chain;
+  if (total == 0 || base == 0xffffffffu) return;
+
+  // The CTA's duplicates are the contiguous run [base, base + total): threads stride over it and
+  // find the owning Gaussian by binary search in the in-block prefix, so writes are coalesced and
+  // a Gaussian covering hundreds of tiles does not serialise one thread.
+  for (uint32_t k = tid; k < total; k += K2_THREADS) {
+    // largest i with s_prefix[i] <= k  (zero-count entries share their successor's prefix and are skipped)
+    uint32_t lo = 0, hi = K2_THREADS;
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
       const uint32_t mid = (lo + hi) >> 1;
-      if (s_prefix[mid] <= j) lo = mid; else hi = mid;
+      if (s_prefix[mid] <= k) lo = mid; else hi = mid;
     }
-    const uint32_t local = j - s_prefix[lo];
-    const uint32_t cols = s_cols[lo];
-    const uint32_t w = cols >> 16;
-    const uint32_t ty = s_row0[lo] + local / w, tx = (cols & 0xffffu) + local % w;
-    const uint32_t tile = ty * (uint32_t)tiles_across + tx;
-    keys[base + j] = ((uint64_t)tile << 32) | s_depth[lo];
-    vals[base + j] = blockIdx.x * K1_THREADS + lo;
+    const uint32_t local = k - s_prefix[lo];
+    const uint32_t cw = s_cols[lo];
+    const uint32_t w = cw >> 16;
+    const uint32_t ty = s_row0[lo] + local / w, tx = (cw & 0xffffu) + local % w;
+    keys[base + k] = ty * (uint32_t)tiles_across + tx;
+    vals[base + k] = s_gauss[lo];
   }
 }
 
-void launch_duplicate(const Projected &p, uint32_t n, const uint32_t *block_offsets, int tiles_across,
-                      uint64_t *keys, uint32_t *vals, uint32_t capacity, uint32_t *overflow, cudaStream_t st) {
+void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t n,
+                      int tiles_across, uint32_t *keys, uint32_t *vals, uint32_t capacity,
+                      unsigned long long *lookback, uint32_t *ticket, uint32_t *total, uint32_t *overflow,
+                      cudaStream_t st) {
   if (!n) return;
   ++g_launches;
-  duplicate_kernel<<<ceil_div(n, K1_THREADS), K1_THREADS, 0, st>>>(p, n, block_offsets, tiles_across, keys, vals,
-                                                                  capacity, overflow);
+  duplicate_kernel<<<ceil_div(n, K2_THREADS), K2_THREADS, 0, st>>>(p, sorted_keys, sorted_gauss, n, tiles_across, keys,
+                                                                  vals, capacity, lookback, ticket, total, overflow);
 }
 
 }  // namespace gsplat

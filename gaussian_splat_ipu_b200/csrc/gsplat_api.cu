@@ -1,5 +1,5 @@
 // gsplat_api.cu — the C ABI of libgsplat_b200.so (include/gsplat_b200.h): context, memory, the
-// per-frame stage sequence K1 -> scan -> K2 -> K3 -> K4 -> K5, read-back.  Host side of what
+// per-frame stage sequence K1 -> sort A -> K2 -> sort B -> K4 -> K5, read-back.  Host side of what
 // splat::IpuSplatter + ipu_utils::GraphManager do for the reference
 // (src/splat/ipu_rasteriser.cpp:49-144,250-420; include/ipu/ipu_utils.hpp:523-623).
 #include "../../include/gsplat_b200.h"
@@ -16,45 +16,60 @@ using namespace gsplat;
 namespace {
 thread_local std::string g_create_error;
 
-enum Ev { EV_START = 0, EV_K1, EV_SCAN, EV_K2, EV_K3, EV_K4, EV_K5, EV_POST0, EV_POST1, EV_T0, EV_T1, EV_COUNT };
+enum Ev { EV_START = 0, EV_K1, EV_SORTA, EV_K2, EV_SORTB, EV_K4, EV_K5, EV_COUNT };
 }  // namespace
+
+// One in-flight frame: its stage events and the pinned words its scalars are copied to.  Frames
+// are enqueued without any host synchronisation; a slot is resolved (event wait, overflow check,
+// timing fold) when it is reused, when a later call needs the frame's results, or opportunistically.
+constexpr int NUM_SLOTS = 4;
+struct FrameSlot {
+  cudaEvent_t ev[EV_COUNT]{};
+  cudaEvent_t done = nullptr;
+  uint32_t *h = nullptr;   // pinned: [0] D  [1] V  [2] overflow
+  bool pending = false, timed = false;
+  uint64_t frame_no = 0;
+};
+
+// device scalars
+enum Scalar { SC_D = 0, SC_V, SC_OVERFLOW, SC_TICKET, SC_N, SC_SORT_N, SC_COUNT = 16 };
 
 struct gsplat_ctx {
   gsplat_config cfg{};
   cudaStream_t st = nullptr;
   std::string err;
-  int tiles_across = 0, tiles_down = 0, num_tiles = 0;
+  int tiles_across = 0, tiles_down = 0, num_tiles = 0, tile_bits = 0;
   // scene
   SceneSoA scene{};
   // per-Gaussian frame buffers
   Projected proj{};
-  uint32_t *block_sums = nullptr;
-  uint32_t n_blocks = 0;
   float *dbg_rec8 = nullptr;
   int32_t *dbg_rect4 = nullptr;
-  // device scalars: [0] D  [1] V  [2] overflow
   uint32_t *d_scalars = nullptr;
-  uint32_t *h_scalars = nullptr;   // pinned mirror
-  // duplicates
-  SortBuffers sort{};
-  int sorted = 0;                  // which of sort.keys/vals holds the sorted result
+  uint32_t *h_scalars = nullptr;   // pinned, NUM_SLOTS * 4 words
+  // sort A: Gaussians by depth (capacity N); sort B: duplicates by tile (capacity grows)
+  SortBuffers sort_a{}, sort_b{};
+  int sorted_a = 0, sorted = 0;    // which of sort_x.keys/vals holds the sorted result
+  unsigned long long *lookback = nullptr;
+  uint32_t n_blocks = 0;
   uint2 *ranges = nullptr;
   uint32_t *counts = nullptr;
   float4 *fb = nullptr;
   uint8_t *bgr = nullptr;
   // state
-  FrameParams fp{};
+  FrameParams fp{};          // set_camera
+  FrameParams frame_fp{};    // camera of the last enqueued frame (re-used when a frame is re-run)
   bool have_scene = false, have_camera = false, have_frame = false;
+  bool last_injected = false;
   gsplat_frame_stats stats{};
-  // stage events are double-buffered by frame parity so that a frame's timings can be folded
-  // into the accumulators at the NEXT frame's mid-frame sync without an extra wait
-  cudaEvent_t ev[2][EV_COUNT]{};
-  int cur_set = 0;
-  bool pending[2] = {false, false}, post_rec[2] = {false, false};
+  FrameSlot slots[NUM_SLOTS];
+  uint64_t frame_no = 0;      // frames enqueued so far; the last one lives in slot (frame_no-1) % NUM_SLOTS
+  size_t need_grow = 0;       // largest D seen by an overflowed frame
+  cudaEvent_t t0 = nullptr, t1 = nullptr, post0 = nullptr, post1 = nullptr;
+  bool post_pending = false;
   float last_ms[GSPLAT_NUM_TIMINGS] = {0};
   double acc_ms[GSPLAT_NUM_TIMINGS] = {0};
   uint64_t acc_frames = 0;
-  int key_bits = 0;
 };
 
 namespace {
@@ -74,23 +89,24 @@ int fail(gsplat_ctx *c, int code, const std::string &msg) {
 template <typename T> void dfree(T *&p) { if (p) { cudaFree(p); p = nullptr; } }
 
 void free_sort(SortBuffers &s) {
-  dfree(s.keys[0]); dfree(s.keys[1]); dfree(s.vals[0]); dfree(s.vals[1]); dfree(s.block_hist); dfree(s.digit_base);
-  s.capacity = 0; s.max_blocks = 0;
+  dfree(s.keys[0]); dfree(s.keys[1]); dfree(s.vals[0]); dfree(s.vals[1]); dfree(s.block_hist); dfree(s.digit_totals);
+  s.capacity = 0; s.max_tiles = 0;
 }
 
-int alloc_sort(gsplat_ctx *ctx, size_t capacity) {
-  if (capacity > 0xfffff000ull) return fail(ctx, GSPLAT_E_CAPACITY, "duplicate count exceeds 32-bit indexing");
+int alloc_sort(gsplat_ctx *ctx, SortBuffers &s, size_t capacity) {
+  if (capacity > 0xfffff000ull) return fail(ctx, GSPLAT_E_CAPACITY, "element count exceeds 32-bit indexing");
   cudaSetDevice(ctx->cfg.device);
-  free_sort(ctx->sort);
-  SortBuffers &s = ctx->sort;
+  free_sort(s);
   capacity = (capacity + RS_TILE - 1) / RS_TILE * RS_TILE;
-  s.max_blocks = (uint32_t)(capacity / RS_TILE);
+  if (capacity == 0) capacity = RS_TILE;
+  s.max_tiles = (uint32_t)(capacity / RS_TILE);
   for (int i = 0; i < 2; ++i) {
-    CU(cudaMalloc(&s.keys[i], capacity * sizeof(uint64_t)));
+    CU(cudaMalloc(&s.keys[i], capacity * sizeof(uint32_t)));
     CU(cudaMalloc(&s.vals[i], capacity * sizeof(uint32_t)));
   }
-  CU(cudaMalloc(&s.block_hist, (size_t)256 * s.max_blocks * sizeof(uint32_t)));
-  CU(cudaMalloc(&s.digit_base, 256 * sizeof(uint32_t)));
+  CU(cudaMalloc(&s.block_hist, (size_t)256 * s.max_tiles * sizeof(uint32_t)));
+  CU(cudaMalloc(&s.digit_totals, 256 * sizeof(uint32_t)));
+  CU(cudaMemset(s.digit_totals, 0, 256 * sizeof(uint32_t)));
   s.capacity = (uint32_t)capacity;
   return GSPLAT_OK;
 }
@@ -128,12 +144,19 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   cudaSetDevice(ctx->cfg.device);
   if (ctx->st) cudaStreamSynchronize(ctx->st);
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
-  dfree(ctx->proj.a); dfree(ctx->proj.b); dfree(ctx->proj.c); dfree(ctx->proj.touched);
-  dfree(ctx->block_sums); dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->d_scalars);
-  free_sort(ctx->sort);
+  dfree(ctx->proj.rec);
+  dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->d_scalars); dfree(ctx->lookback);
+  free_sort(ctx->sort_a); free_sort(ctx->sort_b);
   dfree(ctx->ranges); dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
   if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
-  for (auto &set : ctx->ev) for (auto &e : set) if (e) cudaEventDestroy(e);
+  for (auto &sl : ctx->slots) {
+    for (auto &e : sl.ev) if (e) cudaEventDestroy(e);
+    if (sl.done) cudaEventDestroy(sl.done);
+  }
+  if (ctx->t0) cudaEventDestroy(ctx->t0);
+  if (ctx->t1) cudaEventDestroy(ctx->t1);
+  if (ctx->post0) cudaEventDestroy(ctx->post0);
+  if (ctx->post1) cudaEventDestroy(ctx->post1);
   if (ctx->st) cudaStreamDestroy(ctx->st);
   delete ctx;
 }
@@ -177,10 +200,21 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   } while (0)
   CUC(cudaSetDevice(cfg->device));
   CUC(cudaStreamCreateWithFlags(&ctx->st, cudaStreamNonBlocking));
-  for (auto &set : ctx->ev) for (auto &ev : set) CUC(cudaEventCreate(&ev));
-  CUC(cudaMalloc(&ctx->d_scalars, 16 * sizeof(uint32_t)));
-  CUC(cudaMemset(ctx->d_scalars, 0, 16 * sizeof(uint32_t)));
-  CUC(cudaHostAlloc(&ctx->h_scalars, 16 * sizeof(uint32_t), cudaHostAllocDefault));
+  CUC(cudaHostAlloc(&ctx->h_scalars, NUM_SLOTS * 4 * sizeof(uint32_t), cudaHostAllocDefault));
+  for (int k = 0; k < NUM_SLOTS; ++k) {
+    FrameSlot &sl = ctx->slots[k];
+    for (auto &ev : sl.ev) CUC(cudaEventCreate(&ev));
+    CUC(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    sl.h = ctx->h_scalars + 4 * k;
+  }
+  CUC(cudaEventCreate(&ctx->t0));
+  CUC(cudaEventCreate(&ctx->t1));
+  CUC(cudaEventCreate(&ctx->post0));
+  CUC(cudaEventCreate(&ctx->post1));
+  CUC(cudaMalloc(&ctx->d_scalars, SC_COUNT * sizeof(uint32_t)));
+  CUC(cudaMemset(ctx->d_scalars, 0, SC_COUNT * sizeof(uint32_t)));
+  ctx->tile_bits = ceil_log2((uint32_t)ctx->num_tiles);
+  if (ctx->tile_bits < 1) ctx->tile_bits = 1;
   const size_t px = (size_t)cfg->width * cfg->height;
   CUC(cudaMalloc(&ctx->ranges, sizeof(uint2) * ctx->num_tiles));
   CUC(cudaMalloc(&ctx->counts, sizeof(uint32_t) * ctx->num_tiles));
@@ -200,9 +234,10 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   if (n > 0x7fffffffull) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: too many Gaussians");
   CU(cudaSetDevice(ctx->cfg.device));
   CU(cudaStreamSynchronize(ctx->st));
+  for (auto &sl : ctx->slots) sl.pending = false;
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
-  dfree(ctx->proj.a); dfree(ctx->proj.b); dfree(ctx->proj.c); dfree(ctx->proj.touched);
-  dfree(ctx->block_sums); dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4);
+  dfree(ctx->proj.rec); dfree(ctx->lookback);
+  dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4);
   ctx->have_scene = ctx->have_frame = false;
   const size_t na = n ? n : 1;
   ctx->scene.n = (uint32_t)n;
@@ -210,19 +245,23 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   CU(cudaMalloc(&ctx->scene.quat, na * sizeof(float4)));
   CU(cudaMalloc(&ctx->scene.rgba, na * sizeof(float4)));
   CU(cudaMalloc(&ctx->scene.s12, na * sizeof(float2)));
-  CU(cudaMalloc(&ctx->proj.a, na * sizeof(float4)));
-  CU(cudaMalloc(&ctx->proj.b, na * sizeof(float4)));
-  CU(cudaMalloc(&ctx->proj.c, na * sizeof(float4)));
-  CU(cudaMalloc(&ctx->proj.touched, na * sizeof(uint32_t)));
-  CU(cudaMemsetAsync(ctx->proj.c, 0, na * sizeof(float4), ctx->st));
-  ctx->n_blocks = (uint32_t)((n + K1_THREADS - 1) / K1_THREADS);
-  CU(cudaMalloc(&ctx->block_sums, (ctx->n_blocks + 1) * sizeof(uint32_t)));
+  CU(cudaMalloc(&ctx->proj.rec, na * 3 * sizeof(float4)));
+  CU(cudaMemsetAsync(ctx->proj.rec, 0, na * 3 * sizeof(float4), ctx->st));
+  ctx->n_blocks = (uint32_t)((n + K2_THREADS - 1) / K2_THREADS);
+  CU(cudaMalloc(&ctx->lookback, (ctx->n_blocks + 1) * sizeof(unsigned long long)));
   if (ctx->cfg.debug_records) {
     CU(cudaMalloc(&ctx->dbg_rec8, na * 8 * sizeof(float)));
     CU(cudaMalloc(&ctx->dbg_rect4, na * 4 * sizeof(int32_t)));
   }
+  {  // sort A holds one (depth key, index) pair per Gaussian; K1 writes its keys directly
+    int rc = alloc_sort(ctx, ctx->sort_a, n);
+    if (rc) return rc;
+    ctx->proj.depth_key = ctx->sort_a.keys[0];
+    const uint32_t n32 = (uint32_t)n;
+    CU(cudaMemcpyAsync(ctx->d_scalars + SC_N, &n32, 4, cudaMemcpyHostToDevice, ctx->st));
+    CU(cudaStreamSynchronize(ctx->st));
+  }
   if (n) {
-    // stage the AoS records in the (not yet needed) projected buffers' place: one temporary
     float *tmp = nullptr;
     CU(cudaMalloc(&tmp, n * 16 * sizeof(float)));
     cudaError_t e = cudaMemcpyAsync(tmp, g16, n * 16 * sizeof(float), cudaMemcpyHostToDevice, ctx->st);
@@ -233,9 +272,9 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
     cudaFree(tmp);
     if (e != cudaSuccess) return fail(ctx, GSPLAT_E_CUDA, std::string("scene upload: ") + cudaGetErrorString(e));
   }
-  if (ctx->sort.capacity == 0) {
-    size_t cap = ctx->cfg.dup_capacity ? ctx->cfg.dup_capacity : (n * 3 + (size_t)RS_TILE);
-    int rc = alloc_sort(ctx, cap);
+  if (ctx->sort_b.capacity == 0) {
+    size_t cap = ctx->cfg.dup_capacity ? ctx->cfg.dup_capacity : (n * 4 + (size_t)RS_TILE);
+    int rc = alloc_sort(ctx, ctx->sort_b, cap);
     if (rc) return rc;
   }
   ctx->have_scene = true;

@@ -31,51 +31,64 @@ struct SceneSoA {
   uint32_t n;
 };
 
-// K1 output per Gaussian, 48 B (only the slots of drawn Gaussians are written / read).
+// K1 output per Gaussian: one 48-byte AoS record (three float4, contiguous, so the K5 gather of a
+// record touches two 32 B sectors of one line instead of three lines), written for drawn
+// Gaussians only, plus a 32-bit depth key for EVERY Gaussian (culled = 0xffffffff, sorts last).
+//   rec[3g+0] = mean.x, mean.y, conic.x, conic.y
+//   rec[3g+1] = conic.z, opacity (0 when det == 0), r, g
+//   rec[3g+2] = b, clip z, rect {c0 | c1<<16}, rect {r0 | r1<<16}   (last two are uint bit patterns;
+//               the row pair is already clamped to this context's tile-row band)
 struct Projected {
-  float4 *a;   // mean.x, mean.y, conic.x, conic.y
-  float4 *b;   // conic.z, opacity (0 when det == 0), r, g
-  float4 *c;   // b, clip z, rect {c0 | c1<<16}, rect {r0 | r1<<16}  (last two are uint bit patterns)
-  uint32_t *touched;   // tiles touched (0 = not drawn)
+  float4 *rec;
+  uint32_t *depth_key;   // ~bits(clip z) for drawn Gaussians (z < 0  =>  key < 2^31)
 };
+constexpr uint32_t DEPTH_KEY_CULLED = 0xffffffffu;
 
 constexpr int K1_THREADS = 256;
 
 // ---- launchers (all asynchronous on `st`) ------------------------------------------------
 void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st);
-// K1: writes Projected + per-block sums of `touched` (block_sums[gridDim]).
-void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *block_sums,
-                    uint32_t *drawn_counter, float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st);
-// Debug/parity entry: fill c.{z,rect}/touched from caller-supplied projected inputs.
+// K1: writes Projected; drawn_counter += number of drawn Gaussians (V).
+void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *drawn_counter,
+                    float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st);
+// Debug/parity entry: fill depth key / rect from caller-supplied projected inputs.
 void launch_inject(const float *depth, const int32_t *rect4, const uint8_t *drawn, uint32_t n,
-                   const FrameParams &fp, Projected out, uint32_t *block_sums, uint32_t *drawn_counter,
-                   cudaStream_t st);
-// exclusive scan of block_sums[nblocks] in place; totals[0] = D, totals[1] = V is NOT computed here.
-void launch_scan_block_sums(uint32_t *block_sums, uint32_t nblocks, uint32_t *total, cudaStream_t st);
-// K2: emits (tile<<32 | depth-key, gaussian index) in gid order; sets *overflow if D > capacity.
-void launch_duplicate(const Projected &p, uint32_t n, const uint32_t *block_offsets,
-                      int tiles_across, uint64_t *keys, uint32_t *vals, uint32_t capacity,
-                      uint32_t *overflow, cudaStream_t st);
+                   const FrameParams &fp, Projected out, uint32_t *drawn_counter, cudaStream_t st);
 
-// K3: stable LSD radix sort of the low `key_bits` bits, 8-bit digits.  n is read on the device
-// from *d_n (clamped to capacity).  Result ends in keys_out/vals_out pointers returned.
+// K3: stable LSD radix sort of (u32 key, u32 value) pairs over key bits [begin_bit, end_bit), in
+// ceil(bits/8) digits of equal width.  n is read on the device from *d_n (clamped to capacity).
 struct SortBuffers {
-  uint64_t *keys[2];
+  uint32_t *keys[2];
   uint32_t *vals[2];
-  uint32_t *block_hist;   // 256 * max_blocks
-  uint32_t *digit_base;   // 256
-  uint32_t capacity;      // elements
-  uint32_t max_blocks;
+  uint32_t *block_hist;     // 256 * max_tiles
+  uint32_t *digit_totals;   // 256
+  uint32_t capacity;        // elements
+  uint32_t max_tiles;
 };
 constexpr int RS_THREADS = 256;
 constexpr int RS_ITEMS = 16;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
+constexpr int RS_GRID = 148 * 5;   // CTAs walk RS_TILE-element tiles with a grid stride
+void sort_plan(int nbits, int &passes, int &bits_per_pass);
+// identity_vals: the first digit takes value = element index instead of reading vals[0].
 // returns index (0/1) of the buffer holding the sorted result
-int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int key_bits,
+int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,
+                      bool identity_vals, cudaStream_t st);
+
+// K2: walks the Gaussians in DEPTH order (sorted_gauss = values of sort A) and emits one
+// (tile id, Gaussian index) pair per tile of each drawn Gaussian's rectangle.  Offsets come from a
+// single-pass chained scan (decoupled look-back over `lookback`, which must be zeroed — together
+// with *ticket — before each launch), so the output is in (depth, gid, tile) order and
+// bit-reproducible.  Writes D to *total; sets *overflow (and writes nothing past the buffer) if
+// D > capacity.
+constexpr int K2_THREADS = 256;
+void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t n,
+                      int tiles_across, uint32_t *keys, uint32_t *vals, uint32_t capacity,
+                      unsigned long long *lookback, uint32_t *ticket, uint32_t *total, uint32_t *overflow,
                       cudaStream_t st);
 
-// K4: per-tile [start,end) over the sorted keys.
-void launch_tile_ranges(const uint64_t *keys, const uint32_t *d_n, uint32_t n_upper, uint32_t cap,
+// K4: per-tile [start,end) over the sorted tile keys.
+void launch_tile_ranges(const uint32_t *keys, const uint32_t *d_n, uint32_t n_upper, uint32_t cap,
                         uint2 *ranges, uint32_t num_tiles, cudaStream_t st);
 
 // K5: front-to-back blend of every tile of the band, writes the tile-major f32 framebuffer and

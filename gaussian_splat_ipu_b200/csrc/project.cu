@@ -65,10 +65,9 @@ __device__ __forceinline__ uint32_t clamp_rect(int &c0, int &c1, int &r0, int &r
 }
 
 __global__ void __launch_bounds__(K1_THREADS)
-project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__ block_sums,
-               uint32_t *__restrict__ drawn_counter, float *__restrict__ dbg_rec8,
-               int32_t *__restrict__ dbg_rect4) {
-  __shared__ uint32_t red[2][K1_THREADS / 32];
+project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__ drawn_counter,
+               float *__restrict__ dbg_rec8, int32_t *__restrict__ dbg_rect4) {
+  __shared__ uint32_t red[K1_THREADS / 32];
   const uint32_t i = blockIdx.x * K1_THREADS + threadIdx.x;
   uint32_t touched = 0;
   if (i < s.n) {
@@ -171,14 +170,17 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
             const float det_inv = 1.f / det;
             kx = covc * det_inv; ky = -covb * det_inv; kz = cova * det_inv; kw = col.w;
           }
-          out.a[i] = make_float4(px, py, kx, ky);
-          out.b[i] = make_float4(kz, kw, col.x, col.y);
-          out.c[i] = make_float4(col.z, cz, __uint_as_float((uint32_t)c0 | ((uint32_t)c1 << 16)),
-                                 __uint_as_float((uint32_t)e0 | ((uint32_t)e1 << 16)));
+          float4 *r = out.rec + (size_t)i * 3;
+          r[0] = make_float4(px, py, kx, ky);
+          r[1] = make_float4(kz, kw, col.x, col.y);
+          r[2] = make_float4(col.z, cz, __uint_as_float((uint32_t)c0 | ((uint32_t)c1 << 16)),
+                             __uint_as_float((uint32_t)e0 | ((uint32_t)e1 << 16)));
         }
       }
     }
-    out.touched[i] = touched;
+    // depth key: drawn Gaussians have clip z < 0 (codelets.cpp:493); ascending z (:314) ==
+    // descending magnitude == ascending ~bits(z); everything else sorts last
+    out.depth_key[i] = touched ? ~__float_as_uint(cz) : DEPTH_KEY_CULLED;
     if (dbg_rec8) {
       float4 *d = reinterpret_cast<float4 *>(dbg_rec8 + (size_t)i * 8);
       d[0] = make_float4(px, py, cz, cova);
@@ -186,44 +188,37 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
       reinterpret_cast<int4 *>(dbg_rect4)[i] = make_int4(c0, c1, r0, r1);
     }
   }
-  const uint32_t tot = block_sum<K1_THREADS>(touched, red[0]);
-  const uint32_t nd = block_sum<K1_THREADS>(touched ? 1u : 0u, red[1]);
-  if (threadIdx.x == 0) {
-    block_sums[blockIdx.x] = tot;
-    if (nd) atomicAdd(drawn_counter, nd);
-  }
+  const uint32_t nd = block_sum<K1_THREADS>(touched ? 1u : 0u, red);
+  if (threadIdx.x == 0 && nd) atomicAdd(drawn_counter, nd);
 }
 
 // Parity entry (gsplat_bin_projected): take depth / rect / drawn from the caller instead of K1.
 __global__ void __launch_bounds__(K1_THREADS)
 inject_kernel(const float *__restrict__ depth, const int32_t *__restrict__ rect4,
               const uint8_t *__restrict__ drawn, uint32_t n, FrameParams fp, Projected out,
-              uint32_t *__restrict__ block_sums, uint32_t *__restrict__ drawn_counter) {
-  __shared__ uint32_t red[2][K1_THREADS / 32];
+              uint32_t *__restrict__ drawn_counter) {
+  __shared__ uint32_t red[K1_THREADS / 32];
   const uint32_t i = blockIdx.x * K1_THREADS + threadIdx.x;
   uint32_t touched = 0;
   if (i < n) {
+    float z = 0.f;
     if (drawn[i]) {
       const int4 r = reinterpret_cast<const int4 *>(rect4)[i];
       int c0 = r.x, c1 = r.y, r0 = r.z, r1 = r.w;
       touched = clamp_rect(c0, c1, r0, r1, fp);
       const int e0 = r0 < fp.row_begin ? fp.row_begin : r0, e1 = r1 > fp.row_end - 1 ? fp.row_end - 1 : r1;
       if (touched) {
-        float4 c = out.c[i];
-        c.y = depth[i];
+        float4 c = out.rec[(size_t)i * 3 + 2];
+        c.y = z = depth[i];
         c.z = __uint_as_float((uint32_t)c0 | ((uint32_t)c1 << 16));
         c.w = __uint_as_float((uint32_t)e0 | ((uint32_t)e1 << 16));
-        out.c[i] = c;
+        out.rec[(size_t)i * 3 + 2] = c;
       }
     }
-    out.touched[i] = touched;
+    out.depth_key[i] = touched ? ~__float_as_uint(z) : DEPTH_KEY_CULLED;
   }
-  const uint32_t tot = block_sum<K1_THREADS>(touched, red[0]);
-  const uint32_t nd = block_sum<K1_THREADS>(touched ? 1u : 0u, red[1]);
-  if (threadIdx.x == 0) {
-    block_sums[blockIdx.x] = tot;
-    if (nd) atomicAdd(drawn_counter, nd);
-  }
+  const uint32_t nd = block_sum<K1_THREADS>(touched ? 1u : 0u, red);
+  if (threadIdx.x == 0 && nd) atomicAdd(drawn_counter, nd);
 }
 
 // Scene upload: reference AoS records (16 floats) -> SoA (56 live bytes).
@@ -245,21 +240,19 @@ void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st) {
   aos_to_soa_kernel<<<ceil_div(scene.n, 256), 256, 0, st>>>(reinterpret_cast<const float4 *>(aos16), scene);
 }
 
-void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *block_sums,
-                    uint32_t *drawn_counter, float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st) {
+void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *drawn_counter,
+                    float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st) {
   if (!scene.n) return;
   ++g_launches;
-  project_kernel<<<ceil_div(scene.n, K1_THREADS), K1_THREADS, 0, st>>>(scene, fp, out, block_sums, drawn_counter,
-                                                                      dbg_rec8, dbg_rect4);
+  project_kernel<<<ceil_div(scene.n, K1_THREADS), K1_THREADS, 0, st>>>(scene, fp, out, drawn_counter, dbg_rec8,
+                                                                      dbg_rect4);
 }
 
 void launch_inject(const float *depth, const int32_t *rect4, const uint8_t *drawn, uint32_t n,
-                   const FrameParams &fp, Projected out, uint32_t *block_sums, uint32_t *drawn_counter,
-                   cudaStream_t st) {
+                   const FrameParams &fp, Projected out, uint32_t *drawn_counter, cudaStream_t st) {
   if (!n) return;
   ++g_launches;
-  inject_kernel<<<ceil_div(n, K1_THREADS), K1_THREADS, 0, st>>>(depth, rect4, drawn, n, fp, out, block_sums,
-                                                               drawn_counter);
+  inject_kernel<<<ceil_div(n, K1_THREADS), K1_THREADS, 0, st>>>(depth, rect4, drawn, n, fp, out, drawn_counter);
 }
 
 }  // namespace gsplat

@@ -19,7 +19,8 @@ LIB_PATH = os.path.join(HERE, "libgsplat_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 
 NUM_TIMINGS = 8
-TIMING_NAMES = ("k1_project", "scan", "k2_duplicate", "k3_sort", "k4_ranges", "k5_blend", "post_bgr8", "frame")
+TIMING_NAMES = ("k1_project", "k3a_sort_depth", "k2_duplicate", "k3b_sort_tile", "k4_ranges", "k5_blend", "post_bgr8",
+                "frame")
 
 
 class GsplatError(RuntimeError):
@@ -61,7 +62,7 @@ SYMBOLS = {
     "gsplat_read_projected": (C.c_int, [_vp, _vp, _vp]),
     "gsplat_read_tile_lists": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "gsplat_bin_projected": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int]),
-    "gsplat_sort_pairs": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),
+    "gsplat_sort_pairs": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, C.c_int]),
     "gsplat_host_alloc": (C.c_int, [C.POINTER(_vp), C.c_size_t]),
     "gsplat_host_free": (C.c_int, [_vp]),
     "gsplat_device_framebuffer": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
@@ -267,10 +268,11 @@ class B200Splatter:
         self._check(self.lib.gsplat_bin_projected(self.h, depth.ctypes.data, rect4.ctypes.data, drawn.ctypes.data,
                                                   depth.size, int(blend)))
 
-    def sort_pairs(self, keys, values, key_bits=64):
-        keys = np.ascontiguousarray(keys, np.uint64).copy()
+    def sort_pairs(self, keys, values, begin_bit=0, end_bit=32):
+        keys = np.ascontiguousarray(keys, np.uint32).copy()
         values = np.ascontiguousarray(values, np.uint32).copy()
-        self._check(self.lib.gsplat_sort_pairs(self.h, keys.ctypes.data, values.ctypes.data, keys.size, key_bits))
+        self._check(self.lib.gsplat_sort_pairs(self.h, keys.ctypes.data, values.ctypes.data, keys.size, begin_bit,
+                                               end_bit))
         return keys, values
 
     def device_pointers(self):

@@ -80,7 +80,11 @@ int gsplat_set_camera(gsplat_ctx *ctx, const float modelview[16], const float pr
                       float fov, float scale_div);
 
 /* One run of the "project" program (ipu_rasteriser.cpp:393-399,408-420), converged
- * (SURVEY §8a): K1 project/cull, K2 duplicate, K3 radix sort, K4 tile ranges, K5 blend. */
+ * (SURVEY §8a): K1 project/cull, K3a radix sort of the Gaussians by depth, K2 duplicate (in depth
+ * order), K3b stable radix sort of the duplicates by tile, K4 tile ranges, K5 blend.
+ * Enqueues the whole frame without waiting for the GPU.  If the frame turns out to need more
+ * duplicate slots than allocated, the next gsplat_sync()/gsplat_read_*() grows the buffers and
+ * re-runs it (same camera) before returning, so results that are read are always complete. */
 int gsplat_render(gsplat_ctx *ctx);
 int gsplat_sync(gsplat_ctx *ctx);
 
@@ -104,13 +108,14 @@ typedef struct gsplat_frame_stats {
   uint32_t max_tile_count;
   uint32_t num_tiles;     /* tiles_across * tiles_down                      */
   uint32_t regrown;       /* 1 if this frame had to be re-run after growing */
-  uint32_t key_bits;      /* key bits the radix sort covered                */
+  uint32_t key_bits;      /* sorted key width: 32 depth bits + tile-id bits */
 } gsplat_frame_stats;
 int gsplat_get_frame_stats(gsplat_ctx *ctx, gsplat_frame_stats *out);
 
 /* Stage timings of the last frame in milliseconds (needs collect_timings):
- * [0] K1 project  [1] offsets scan  [2] K2 duplicate  [3] K3 sort  [4] K4 ranges  [5] K5 blend
- * [6] BGR8 post (last read_framebuffer_bgr8)  [7] whole frame.  Returns the count written. */
+ * [0] K1 project  [1] K3a depth sort  [2] K2 duplicate  [3] K3b tile sort  [4] K4 ranges
+ * [5] K5 blend  [6] BGR8 post (last read_framebuffer_bgr8)  [7] whole frame.
+ * Returns the count written. */
 #define GSPLAT_NUM_TIMINGS 8
 int gsplat_get_timings(gsplat_ctx *ctx, float *ms, int capacity);
 /* Sums of the same GSPLAT_NUM_TIMINGS stage timings over all frames rendered since the last reset
@@ -130,9 +135,11 @@ int gsplat_read_tile_lists(gsplat_ctx *ctx, int64_t *offsets, int32_t *lists, si
  * gsplat_render().  "Per-tile lists bit-exact given identical projected inputs". */
 int gsplat_bin_projected(gsplat_ctx *ctx, const float *depth, const int32_t *rect4,
                          const uint8_t *drawn, size_t n, int blend);
-/* Stand-alone run of the K3 device radix sort on caller data: stable sort on the low key_bits
- * bits, rounded UP to whole 8-bit digits (17 -> 24).  Used by the sort known-answer tests. */
-int gsplat_sort_pairs(gsplat_ctx *ctx, uint64_t *keys, uint32_t *values, size_t n, int key_bits);
+/* Stand-alone run of the K3 device radix sort on caller data: stable sort of (key, value) pairs
+ * on key bits [begin_bit, end_bit) only, in ceil(bits/8) digits of equal width.  Used by the sort
+ * known-answer tests. */
+int gsplat_sort_pairs(gsplat_ctx *ctx, uint32_t *keys, uint32_t *values, size_t n, int begin_bit,
+                      int end_bit);
 
 /* ---- helpers ------------------------------------------------------------------------------- */
 /* Pinned host memory for frame read-back buffers (cudaHostAlloc / cudaFreeHost). */
