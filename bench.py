@@ -39,6 +39,7 @@ DEFAULT_WORKLOAD = "synthetic-6M-1080p"
 ORBIT_VIEWS = 64
 FOV = sc.DEFAULT_FOV
 SCALE_DIV = 1.0
+REF_BUDGET_S = 120.0   # wall-clock bound on the timed frames of the CPU reference arm
 
 
 def make_scene(name):
@@ -56,19 +57,31 @@ def view_for(base, k):
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons of one GPU during the timed region (NVML)."""
+    """Samples SM clock and throttle reasons of one GPU during the timed region (NVML).  NVML is
+    initialised and the queries are warmed up at construction — the first calls take milliseconds
+    and would otherwise stall kernel launches inside the timed region; `arm()` starts sampling."""
 
-    def __init__(self, index):
+    def __init__(self, index, period=0.02):
         super().__init__(daemon=True)
-        self.index, self.samples, self.reasons, self.max_mhz, self._stop_ev = index, [], set(), None, threading.Event()
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self.period, self._stop_ev, self._armed = period, threading.Event(), threading.Event()
         try:
+            if os.environ.get("GSPLAT_BENCH_NO_SAMPLER"):
+                raise RuntimeError("sampler disabled")
             import pynvml
             pynvml.nvmlInit()
             self.nv = pynvml
             self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
             self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            for _ in range(3):
+                pynvml.nvmlDeviceGetClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
         except Exception:
             self.nv = None
+        self.start()
+
+    def arm(self):
+        self._armed.set()
 
     def run(self):
         if self.nv is None:
@@ -78,6 +91,7 @@ class ClockSampler(threading.Thread):
                  nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
                  nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
                  nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        self._armed.wait()
         while not self._stop_ev.is_set():
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
@@ -87,10 +101,11 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(nm)
             except Exception:
                 pass
-            self._stop_ev.wait(0.05)
+            self._stop_ev.wait(self.period)
 
     def finish(self):
         self._stop_ev.set()
+        self._armed.set()
         self.join(timeout=2)
         med = float(np.median(self.samples)) if self.samples else None
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
@@ -128,23 +143,27 @@ def reference_arm(args):
     kind = "reference" if pyoracle.have_ref() else "port"
     g, base, proj, W, H = make_scene(args.workload)
     n = g.shape[0]
-    # bounded sample: one step = one frame of the same scene/camera orbit on ALL host threads
+    # bounded sample: one step = one full frame of the same scene/camera orbit on ALL host threads;
+    # a CPU frame takes seconds, so at most REF_BUDGET_S seconds of timed frames are run (>= 2) and
+    # the line says how many of the requested steps that was
     times = []
     cores = 0
-    for k in range(args.warmup + args.steps):
-        dt, cores, _ = cpu_frame_time(kind, g, view_for(base, k), proj, W, H)
-        if k >= args.warmup:
-            times.append(dt)
+    dt, cores, _ = cpu_frame_time(kind, g, view_for(base, 0), proj, W, H)          # warm-up (1 frame)
+    steps = max(2, min(args.steps, int(REF_BUDGET_S / max(dt, 1e-3))))
+    for k in range(steps):
+        dt, cores, _ = cpu_frame_time(kind, g, view_for(base, args.warmup + k), proj, W, H)
+        times.append(dt)
     total = float(np.sum(times))
-    fps = args.steps / total
+    fps = steps / total
     line = {"impl": "reference", "metric": "frames_per_second", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "gaussians": n, "width": W, "height": H, "tile": "32x20",
-                       "scale_div": SCALE_DIV, "views": "orbit"},
+                       "scale_div": SCALE_DIV, "views": "orbit"}, "steps_timed": steps,
             "mgaussians_per_s": n * fps / 1e6,
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
-                             "sample": f"{args.steps} full frames of {args.workload}, all host threads (OpenMP)"},
+                             "sample": f"{steps} full frames of {args.workload} (of {args.steps} requested steps; "
+                                       f"{REF_BUDGET_S:.0f} s bound), all host threads (OpenMP)"},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -206,8 +225,12 @@ def gpu_arm(args):
     s.updateProjection(proj)
     s.updateFocalLengths(FOV, SCALE_DIV)
 
+    # camera matrices are host inputs: build the orbit once so the timed loops measure the render
+    # path, not numpy
+    views = [view_for(base, k) for k in range(ORBIT_VIEWS)]
+
     def step(k):
-        s.updateModelView(view_for(base, k * world + rank))
+        s.updateModelView(views[(k * world + rank) % ORBIT_VIEWS])
         s.execute()
 
     K, Wm = args.steps, args.warmup
@@ -219,7 +242,7 @@ def gpu_arm(args):
     # ---- device-resident leg: scene in HBM, K frames back to back -----------------------------
     sampler = ClockSampler(local)
     barrier()
-    sampler.start()
+    sampler.arm()
     l0 = launch_count()
     t0 = time.perf_counter()
     s.timer_begin()
@@ -297,8 +320,8 @@ def gpu_arm(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -60,34 +60,60 @@ __device__ __forceinline__ void st_relaxed(unsigned long long *p, unsigned long 
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// One CTA = one link of the chain = K2_CHUNK consecutive positions of the depth order
+// (K2_ITEMS per thread, striped so the loads coalesce and the rectangle gathers overlap).
+struct K2Smem {
+  uint32_t prefix[K2_CHUNK + 1];
+  uint32_t gauss[K2_CHUNK];
+  uint32_t cols[K2_CHUNK];   // c0 | width << 16
+  uint32_t row0[K2_CHUNK];
+  uint32_t wt[K2_THREADS / 32 + 1];
+  uint32_t chain;            // this CTA's position in the chain, then its base offset
+};
+
 __global__ void __launch_bounds__(K2_THREADS)
 duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const uint32_t *__restrict__ sorted_gauss,
                  uint32_t n, int tiles_across, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals,
                  uint32_t capacity, unsigned long long *__restrict__ lookback, uint32_t *__restrict__ ticket,
                  uint32_t *__restrict__ total_out, uint32_t *__restrict__ overflow) {
-  __shared__ uint32_t wt[K2_THREADS / 32 + 1];
-  __shared__ uint32_t s_prefix[K2_THREADS + 1];
-  __shared__ uint32_t s_gauss[K2_THREADS];
-  __shared__ uint32_t s_cols[K2_THREADS];   // c0 | width << 16
-  __shared__ uint32_t s_row0[K2_THREADS];
-  __shared__ uint32_t s_chain;              // this CTA's position in the chain, then its base offset
+  extern __shared__ __align__(16) unsigned char k2_smem_raw[];
+  K2Smem &sm = *reinterpret_cast<K2Smem *>(k2_smem_raw);
   const uint32_t tid = threadIdx.x;
-  if (tid == 0) s_chain = atomicAdd(ticket, 1u);
+  if (tid == 0) sm.chain = atomicAdd(ticket, 1u);
   __syncthreads();
-  const uint32_t b = s_chain;
-  const uint32_t j = b * K2_THREADS + tid;   // position in depth order
-  uint32_t t = 0, g = 0, cols = 0, row0 = 0;
-  if (j < n && sorted_keys[j] != DEPTH_KEY_CULLED) {
-    g = sorted_gauss[j];
-    const float4 c = __ldg(&p.rec[(size_t)g * 3 + 2]);
-    const uint32_t cw = __float_as_uint(c.z), rw = __float_as_uint(c.w);
-    const uint32_t c0 = cw & 0xffffu, c1 = cw >> 16, r0 = rw & 0xffffu, r1 = rw >> 16;
-    cols = c0 | ((c1 - c0 + 1) << 16);
-    row0 = r0;
-    t = (c1 - c0 + 1) * (r1 - r0 + 1);
+  const uint32_t b = sm.chain;
+  uint32_t g[K2_ITEMS];
+  bool live[K2_ITEMS];
+#pragma unroll
+  for (int i = 0; i < K2_ITEMS; ++i) {
+    const uint32_t j = b * K2_CHUNK + i * K2_THREADS + tid;   // position in depth order
+    live[i] = j < n && sorted_keys[j] != DEPTH_KEY_CULLED;
+    g[i] = live[i] ? sorted_gauss[j] : 0u;
   }
+#pragma unroll
+  for (int i = 0; i < K2_ITEMS; ++i) {
+    const uint32_t e = i * K2_THREADS + tid;
+    uint32_t t = 0, cols = 0, row0 = 0;
+    if (live[i]) {
+      const float4 c = __ldg(&p.rec[(size_t)g[i] * 3 + 2]);
+      const uint32_t cw = __float_as_uint(c.z), rw = __float_as_uint(c.w);
+      const uint32_t c0 = cw & 0xffffu, c1 = cw >> 16, r0 = rw & 0xffffu, r1 = rw >> 16;
+      cols = c0 | ((c1 - c0 + 1) << 16);
+      row0 = r0;
+      t = (c1 - c0 + 1) * (r1 - r0 + 1);
+    }
+    sm.prefix[e] = t; sm.gauss[e] = g[i]; sm.cols[e] = cols; sm.row0[e] = row0;
+  }
+  __syncthreads();
+  // exclusive scan of the chunk in position order: thread tid owns entries [tid*ITEMS, (tid+1)*ITEMS)
+  uint32_t loc[K2_ITEMS], sum = 0;
+#pragma unroll
+  for (int i = 0; i < K2_ITEMS; ++i) { loc[i] = sm.prefix[tid * K2_ITEMS + i]; sum += loc[i]; }
   uint32_t total;
-  const uint32_t ex = block_excl_scan<K2_THREADS>(t, wt, total);
+  uint32_t ex = block_excl_scan<K2_THREADS>(sum, sm.wt, total);
+#pragma unroll
+  for (int i = 0; i < K2_ITEMS; ++i) { sm.prefix[tid * K2_ITEMS + i] = ex; ex += loc[i]; }
+  if (tid == 0) sm.prefix[K2_CHUNK] = total;
 
   // ---- chained scan: publish the aggregate, look back for the exclusive prefix ------------------
   if (tid < 32) {
@@ -118,33 +144,30 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
       const unsigned long long incl = excl + total;
       if (b == gridDim.x - 1) *total_out = incl > 0xffffffffull ? 0xffffffffu : (uint32_t)incl;
       if (incl > capacity) atomicExch(overflow, 1u);   // never write past the buffer; the host re-runs
-      s_chain = incl > capacity ? 0xffffffffu : (uint32_t)excl;
+      sm.chain = incl > capacity ? 0xffffffffu : (uint32_t)excl;
     }
   }
-  s_prefix[tid] = ex;
-  if (tid == 0) s_prefix[K2_THREADS] = total;
-  s_gauss[tid] = g; s_cols[tid] = cols; s_row0[tid] = row0;
   __syncthreads();
-  const uint32_t base = s_chain;
+  const uint32_t base = sm.chain;
   if (total == 0 || base == 0xffffffffu) return;
 
   // The CTA's duplicates are the contiguous run [base, base + total): threads stride over it and
-  // find the owning Gaussian by binary search in the in-block prefix, so writes are coalesced and
+  // find the owning Gaussian by binary search in the chunk prefix, so writes are coalesced and
   // a Gaussian covering hundreds of tiles does not serialise one thread.
   for (uint32_t k = tid; k < total; k += K2_THREADS) {
-    // largest i with s_prefix[i] <= k  (zero-count entries share their successor's prefix and are skipped)
-    uint32_t lo = 0, hi = K2_THREADS;
+    // largest i with prefix[i] <= k  (zero-count entries share their successor's prefix and are skipped)
+    uint32_t lo = 0, hi = K2_CHUNK;
 #pragma unroll
-    for (int s = 0; s < 8; ++s) {
+    for (int s = 0; s < K2_LOG_CHUNK; ++s) {
       const uint32_t mid = (lo + hi) >> 1;
-      if (s_prefix[mid] <= k) lo = mid; else hi = mid;
+      if (sm.prefix[mid] <= k) lo = mid; else hi = mid;
     }
-    const uint32_t local = k - s_prefix[lo];
-    const uint32_t cw = s_cols[lo];
+    const uint32_t local = k - sm.prefix[lo];
+    const uint32_t cw = sm.cols[lo];
     const uint32_t w = cw >> 16;
-    const uint32_t ty = s_row0[lo] + local / w, tx = (cw & 0xffffu) + local % w;
+    const uint32_t ty = sm.row0[lo] + local / w, tx = (cw & 0xffffu) + local % w;
     keys[base + k] = ty * (uint32_t)tiles_across + tx;
-    vals[base + k] = s_gauss[lo];
+    vals[base + k] = sm.gauss[lo];
   }
 }
 
@@ -153,8 +176,13 @@ void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uin
                       unsigned long long *lookback, uint32_t *ticket, uint32_t *total, uint32_t *overflow,
                       cudaStream_t st) {
   if (!n) return;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(duplicate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem));
+    attr_set = true;
+  }
   ++g_launches;
-  duplicate_kernel<<<ceil_div(n, K2_THREADS), K2_THREADS, 0, st>>>(p, sorted_keys, sorted_gauss, n, tiles_across, keys,
+  duplicate_kernel<<<ceil_div(n, K2_CHUNK), K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_keys, sorted_gauss, n, tiles_across, keys,
                                                                   vals, capacity, lookback, ticket, total, overflow);
 }
 

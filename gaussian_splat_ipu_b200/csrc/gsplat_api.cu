@@ -247,7 +247,7 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   CU(cudaMalloc(&ctx->scene.s12, na * sizeof(float2)));
   CU(cudaMalloc(&ctx->proj.rec, na * 3 * sizeof(float4)));
   CU(cudaMemsetAsync(ctx->proj.rec, 0, na * 3 * sizeof(float4), ctx->st));
-  ctx->n_blocks = (uint32_t)((n + K2_THREADS - 1) / K2_THREADS);
+  ctx->n_blocks = (uint32_t)((n + K2_CHUNK - 1) / K2_CHUNK);
   CU(cudaMalloc(&ctx->lookback, (ctx->n_blocks + 1) * sizeof(unsigned long long)));
   if (ctx->cfg.debug_records) {
     CU(cudaMalloc(&ctx->dbg_rec8, na * 8 * sizeof(float)));

@@ -56,7 +56,7 @@ void launch_inject(const float *depth, const int32_t *rect4, const uint8_t *draw
                    const FrameParams &fp, Projected out, uint32_t *drawn_counter, cudaStream_t st);
 
 // K3: stable LSD radix sort of (u32 key, u32 value) pairs over key bits [begin_bit, end_bit), in
-// ceil(bits/8) digits of equal width.  n is read on the device from *d_n (clamped to capacity).
+// ceil(bits/7) digits of equal width.  n is read on the device from *d_n (clamped to capacity).
 struct SortBuffers {
   uint32_t *keys[2];
   uint32_t *vals[2];
@@ -68,7 +68,8 @@ struct SortBuffers {
 constexpr int RS_THREADS = 256;
 constexpr int RS_ITEMS = 16;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
-constexpr int RS_GRID = 148 * 5;   // CTAs walk RS_TILE-element tiles with a grid stride
+constexpr int RS_MAX_BITS = 7;      // digit width limit of the counter-based ranking (128 digits)
+constexpr int RS_GRID = 148 * 3;   // CTAs walk RS_TILE-element tiles with a grid stride
 void sort_plan(int nbits, int &passes, int &bits_per_pass);
 // identity_vals: the first digit takes value = element index instead of reading vals[0].
 // returns index (0/1) of the buffer holding the sorted result
@@ -82,6 +83,10 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
 // bit-reproducible.  Writes D to *total; sets *overflow (and writes nothing past the buffer) if
 // D > capacity.
 constexpr int K2_THREADS = 256;
+constexpr int K2_ITEMS = 8;
+constexpr int K2_LOG_CHUNK = 11;
+constexpr int K2_CHUNK = K2_THREADS * K2_ITEMS;   // Gaussians per CTA == per chain link
+static_assert((1 << K2_LOG_CHUNK) == K2_CHUNK, "binary search depth");
 void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t n,
                       int tiles_across, uint32_t *keys, uint32_t *vals, uint32_t capacity,
                       unsigned long long *lookback, uint32_t *ticket, uint32_t *total, uint32_t *overflow,

@@ -4,7 +4,7 @@
 // The reference orders each tile's list with a per-tile quicksort by clip z
 // (codelets/splat/codelets.cpp:303-356) after its lattice has routed Gaussians to tiles.  Here the
 // same order — (tile, z ascending, gid ascending) — comes from TWO uses of this one sort:
-//   sort A  the N Gaussians by their 32-bit depth key (4 digits of 8 bits), values = Gaussian index
+//   sort A  the N Gaussians by their 32-bit depth key (5 digits of 7/6 bits), values = Gaussian index
 //   sort B  the D (tile, Gaussian) duplicates, emitted by K2 in depth order, by tile id only
 //           (ceil(log2(tiles)) bits: 2 digits of 6 bits at 1080p, of 7 bits at 4K)
 // Both are stable, so sort B keeps the depth order inside every tile: the result is exactly what a
@@ -15,7 +15,7 @@
 // tiles -> ranked scatter.  "Tile" here = RS_TILE consecutive elements; CTAs walk tiles with a grid
 // stride and the element count is read on the device (*d_n), so the host never needs to know N or
 // D to launch the sort (no mid-frame synchronisation).  HBM-bound: 4 B (hist) + 8 B + 8 B (scatter)
-// per element per digit.
+// per element per digit; digits are at most RS_MAX_BITS = 7 bits wide.
 #include "gsplat_internal.h"
 
 namespace gsplat {
@@ -33,33 +33,117 @@ __device__ __forceinline__ uint32_t num_elems(const uint32_t *d_n, uint32_t cap)
 
 constexpr int RS_WARPS = RS_THREADS / 32;
 
+// Ranking uses per-thread digit counters in shared memory (no warp votes, no atomics): every
+// thread owns RS_ITEMS CONSECUTIVE elements of the tile and bumps a private 16-bit counter per
+// digit; a raking scan over all counters in (digit, thread) order then turns "count so far in my
+// thread" into the element's stable position inside the tile.  Two digits share a 32-bit word
+// (digit d and d + LANES, LANES = radix / 2), so the scan adds whole words: no half can overflow
+// because a tile has 4096 < 65536 elements.  Word (lane, thread) lives at PAD(lane * 256 + thread);
+// the padding (one word per 32) keeps both the per-thread bumps and the raking segments
+// bank-conflict free.
+__device__ __forceinline__ uint32_t rs_pad(uint32_t i) { return i + (i >> 5); }
+constexpr uint32_t rs_counter_words(int bits) {
+  const uint32_t w = (uint32_t)RS_THREADS << (bits > 1 ? bits - 1 : 0);
+  return w + (w >> 5);
+}
+
+// exclusive scan of one value per thread over the 256-thread CTA; *total = sum (all threads)
+__device__ __forceinline__ uint32_t cta_excl_scan256(uint32_t v, uint32_t *wt, uint32_t lane, uint32_t warp,
+                                                     uint32_t *total = nullptr) {
+  uint32_t inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) wt[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t t = lane < RS_WARPS ? wt[lane] : 0, ti = t;
+#pragma unroll
+    for (int o = 1; o < RS_WARPS; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, ti, o);
+      if (lane >= o) ti += u;
+    }
+    if (lane < RS_WARPS) wt[lane] = ti - t;
+    if (lane == RS_WARPS - 1) wt[RS_WARPS] = ti;
+  }
+  __syncthreads();
+  const uint32_t r = wt[warp] + inc - v;
+  if (total) *total = wt[RS_WARPS];
+  __syncthreads();
+  return r;
+}
+
+// Loads the RS_ITEMS consecutive keys this thread owns (blocked arrangement); elements past n get
+// the all-ones key, which ranks after every valid element of the tile.
+__device__ __forceinline__ void rs_load_blocked(const uint32_t *__restrict__ src, uint32_t first, uint32_t n,
+                                                uint32_t fill, uint32_t (&out)[RS_ITEMS]) {
+  if (first + RS_ITEMS <= n) {
+    const uint4 *p = reinterpret_cast<const uint4 *>(src + first);
+#pragma unroll
+    for (int q = 0; q < RS_ITEMS / 4; ++q) {
+      const uint4 v = p[q];
+      out[q * 4 + 0] = v.x; out[q * 4 + 1] = v.y; out[q * 4 + 2] = v.z; out[q * 4 + 3] = v.w;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) out[k] = first + k < n ? src[first + k] : fill;
+  }
+}
+
+// byte offset of the 16-bit counter of digit d for this thread
+__device__ __forceinline__ uint32_t rs_counter_off(uint32_t d, uint32_t lanes_mask, int lanes_log, uint32_t tid) {
+  const uint32_t lane = d & lanes_mask, sub = d >> lanes_log;
+  return rs_pad(lane * RS_THREADS + tid) * 4u + sub * 2u;
+}
+
 // ---- digit histogram of every tile -----------------------------------------------------------
 __global__ void __launch_bounds__(RS_THREADS)
 rs_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ d_n, uint32_t cap, int shift,
-               uint32_t mask, uint32_t *__restrict__ block_hist, uint32_t stride) {
-  __shared__ uint32_t warp_hist[RS_WARPS][256];
+               int bits, uint32_t *__restrict__ block_hist, uint32_t stride) {
+  extern __shared__ __align__(16) uint32_t rs_cnt[];
   const uint32_t n = num_elems(d_n, cap);
   const uint32_t ntiles = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
-  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t tid = threadIdx.x;
+  const uint32_t mask = (1u << bits) - 1u;
+  const int lanes_log = bits > 1 ? bits - 1 : 0;
+  const uint32_t lanes = 1u << lanes_log, lanes_mask = lanes - 1u;
+  const uint32_t words = rs_pad(lanes * RS_THREADS);
+  // reduction mapping: thread = (counter lane, part); each sums `span` threads' packed words
+  const uint32_t parts = lanes >= RS_THREADS ? 1u : RS_THREADS / lanes;   // power of two
+  const uint32_t span = RS_THREADS / parts;
+  const uint32_t r_lane = tid / parts, r_part = tid % parts;
+  unsigned char *cbytes = reinterpret_cast<unsigned char *>(rs_cnt);
   for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-    for (int k = tid; k < RS_WARPS * 256; k += RS_THREADS) (&warp_hist[0][0])[k] = 0;
+    for (uint32_t k = tid; k < words; k += RS_THREADS) rs_cnt[k] = 0;
     __syncthreads();
-    const uint32_t seg = t * RS_TILE + warp * (32 * RS_ITEMS);
-#pragma unroll 4
+    uint32_t key[RS_ITEMS];
+    const uint32_t first = t * RS_TILE + tid * RS_ITEMS;
+    rs_load_blocked(keys, first, n, 0xffffffffu, key);
+#pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
-      const uint32_t idx = seg + k * 32 + lane;
-      const bool valid = idx < n;
-      const uint32_t d = valid ? (keys[idx] >> shift) & mask : 256u;
-      const uint32_t m = __match_any_sync(0xffffffffu, d);
-      if (valid && (m & lanemask_lt()) == 0) warp_hist[warp][d] += __popc(m);   // group leader
-      __syncwarp();
+      if (first + k < n) {
+        unsigned short *c = reinterpret_cast<unsigned short *>(
+            cbytes + rs_counter_off((key[k] >> shift) & mask, lanes_mask, lanes_log, tid));
+        *c = *c + 1;
+      }
     }
     __syncthreads();
-    if (tid <= mask) {
-      uint32_t c = 0;
-#pragma unroll
-      for (int w = 0; w < RS_WARPS; ++w) c += warp_hist[w][tid];
-      block_hist[(size_t)tid * stride + t] = c;
+    uint32_t sum = 0;   // packed: low half = digit r_lane, high half = digit r_lane + lanes
+    if (r_lane < lanes)
+      for (uint32_t i = 0; i < span; ++i) sum += rs_cnt[rs_pad(r_lane * RS_THREADS + r_part * span + i)];
+    for (uint32_t o = 1; o < parts && o < 32; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (parts > 32) {   // only for 1- and 2-bit digits: finish across warps through shared memory
+      __syncthreads();
+      if ((tid & 31) == 0) rs_cnt[tid >> 5] = sum;
+      __syncthreads();
+      sum = 0;
+      if (r_part == 0) for (uint32_t w = 0; w < parts / 32; ++w) sum += rs_cnt[r_lane * (parts / 32) + w];
+    }
+    if (r_part == 0 && r_lane < lanes) {
+      block_hist[(size_t)r_lane * stride + t] = sum & 0xffffu;
+      if (bits > 0 && r_lane + lanes <= mask) block_hist[(size_t)(r_lane + lanes) * stride + t] = sum >> 16;
     }
     __syncthreads();
   }
@@ -105,121 +189,103 @@ rs_scan_kernel(uint32_t *__restrict__ block_hist, uint32_t stride, const uint32_
 }
 
 // ---- stable ranked scatter ---------------------------------------------------------------------
-// Key order inside a tile: warp w owns the contiguous segment [w*512, (w+1)*512), item k / lane l
-// is element k*32 + l of it, so (warp, k, lane) order == memory order and ranks are stable.
-struct RsSmem {
-  uint32_t keys[RS_TILE];
-  uint32_t vals[RS_TILE];
-  uint32_t warp_hist[RS_WARPS][256];
-  uint32_t tile_start[256];
-  uint32_t out_base[256];
+// Dynamic shared memory: the counter words, re-used as the (key, value) staging area once every
+// element knows its position; then out_base[128] and the scan scratch.
+struct RsTail {
+  uint32_t out_base[128];
   uint32_t wt[RS_WARPS + 1];
 };
-
-// exclusive scan of one value per thread over the 256-thread CTA (result for every thread)
-__device__ __forceinline__ uint32_t cta_excl_scan256(uint32_t v, uint32_t *wt, uint32_t lane, uint32_t warp) {
-  uint32_t inc = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += t;
-  }
-  if (lane == 31) wt[warp] = inc;
-  __syncthreads();
-  if (warp == 0) {
-    uint32_t t = lane < RS_WARPS ? wt[lane] : 0, ti = t;
-#pragma unroll
-    for (int o = 1; o < RS_WARPS; o <<= 1) {
-      const uint32_t u = __shfl_up_sync(0xffffffffu, ti, o);
-      if (lane >= o) ti += u;
-    }
-    if (lane < RS_WARPS) wt[lane] = ti - t;
-  }
-  __syncthreads();
-  const uint32_t r = wt[warp] + inc - v;
-  __syncthreads();
-  return r;
+constexpr size_t rs_scatter_smem(int bits) {
+  const size_t counters = (size_t)rs_counter_words(bits) * 4, staging = (size_t)RS_TILE * 8;
+  return (counters > staging ? counters : staging) + sizeof(RsTail);
 }
 
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, 3)
 rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                   uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
-                  const uint32_t *__restrict__ d_n, uint32_t cap, int shift, uint32_t mask,
+                  const uint32_t *__restrict__ d_n, uint32_t cap, int shift, int bits, uint32_t body_bytes,
                   const uint32_t *__restrict__ block_hist, uint32_t stride,
                   const uint32_t *__restrict__ digit_totals) {
-  extern __shared__ __align__(16) unsigned char rs_smem_raw[];
-  RsSmem &sm = *reinterpret_cast<RsSmem *>(rs_smem_raw);
+  extern __shared__ __align__(16) uint32_t rs_cnt[];
+  unsigned char *cbytes = reinterpret_cast<unsigned char *>(rs_cnt);
+  uint2 *stage = reinterpret_cast<uint2 *>(rs_cnt);
+  RsTail &tail = *reinterpret_cast<RsTail *>(cbytes + body_bytes);
   const uint32_t n = num_elems(d_n, cap);
   const uint32_t ntiles = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t lt = lanemask_lt();
+  const uint32_t mask = (1u << bits) - 1u;
+  const int lanes_log = bits > 1 ? bits - 1 : 0;
+  const uint32_t lanes = 1u << lanes_log, lanes_mask = lanes - 1u;
+  const uint32_t words = rs_pad(lanes * RS_THREADS);
   // global base of digit `tid`: exclusive scan of the digit totals (same for every tile)
   const uint32_t dt = tid <= mask ? digit_totals[tid] : 0;
-  const uint32_t dbase = cta_excl_scan256(dt, sm.wt, lane, warp);
+  const uint32_t dbase = cta_excl_scan256(dt, tail.wt, lane, warp);
 
   for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const uint32_t tile_n = min((uint32_t)RS_TILE, n - t * RS_TILE);
-    for (int k = tid; k < RS_WARPS * 256; k += RS_THREADS) (&sm.warp_hist[0][0])[k] = 0;
+    for (uint32_t k = tid; k < words; k += RS_THREADS) rs_cnt[k] = 0;
     __syncthreads();
 
-    uint32_t key[RS_ITEMS];
-    uint32_t rank[RS_ITEMS];
-    const uint32_t seg = t * RS_TILE + warp * (32 * RS_ITEMS);
+    uint32_t key[RS_ITEMS], val[RS_ITEMS], pos[RS_ITEMS];
+    const uint32_t first = t * RS_TILE + tid * RS_ITEMS;
+    rs_load_blocked(keys_in, first, n, 0xffffffffu, key);
+    if (vals_in) rs_load_blocked(vals_in, first, n, 0u, val);
+    else {   // first digit of sort A: value = element index
 #pragma unroll
-    for (int k = 0; k < RS_ITEMS; ++k) {
-      const uint32_t idx = seg + k * 32 + lane;
-      key[k] = idx < n ? keys_in[idx] : 0xffffffffu;
+      for (int k = 0; k < RS_ITEMS; ++k) val[k] = first + k;
     }
+    // count: pos[k] = how many earlier elements of THIS thread have the same digit
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
-      const bool valid = seg + k * 32 + lane < n;
-      const uint32_t d = valid ? (key[k] >> shift) & mask : 256u;
-      const uint32_t m = __match_any_sync(0xffffffffu, d);
-      const int leader = __ffs(m) - 1;
-      uint32_t old = 0;
-      if (valid && (int)lane == leader) {
-        old = sm.warp_hist[warp][d];
-        sm.warp_hist[warp][d] = old + __popc(m);
-      }
-      old = __shfl_sync(0xffffffffu, old, leader);
-      rank[k] = old + __popc(m & lt);
-      __syncwarp();
+      unsigned short *c = reinterpret_cast<unsigned short *>(
+          cbytes + rs_counter_off((key[k] >> shift) & mask, lanes_mask, lanes_log, tid));
+      const uint32_t r = *c;
+      *c = (unsigned short)(r + 1);
+      pos[k] = r;
     }
     __syncthreads();
 
-    // digit `tid`: exclusive scan over warps, tile count, then exclusive scan over digits
-    uint32_t cnt = 0;
-#pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) {
-      const uint32_t c = sm.warp_hist[w][tid];
-      sm.warp_hist[w][tid] = cnt;
-      cnt += c;
-    }
-    const uint32_t tstart = cta_excl_scan256(cnt, sm.wt, lane, warp);
-    sm.tile_start[tid] = tstart;
-    sm.out_base[tid] = tid <= mask ? dbase + block_hist[(size_t)tid * stride + t] - tstart : 0;
-    __syncthreads();
-
-    // reorder through shared memory so the global writes are runs of equal digits
-#pragma unroll
-    for (int k = 0; k < RS_ITEMS; ++k) {
-      const uint32_t idx = seg + k * 32 + lane;
-      if (idx < n) {
-        const uint32_t d = (key[k] >> shift) & mask;
-        const uint32_t pos = sm.tile_start[d] + sm.warp_hist[warp][d] + rank[k];
-        sm.keys[pos] = key[k];
-        sm.vals[pos] = vals_in ? vals_in[idx] : idx;   // first digit of sort A: value = index
+    // raking scan over all counter words in (counter lane, thread) order: thread `tid` owns the
+    // `lanes` consecutive words starting at tid * lanes
+    {
+      const uint32_t w0 = tid * lanes;
+      uint32_t sum = 0;
+      for (uint32_t i = 0; i < lanes; ++i) sum += rs_cnt[rs_pad(w0 + i)];
+      uint32_t total;
+      uint32_t run = cta_excl_scan256(sum, tail.wt, lane, warp, &total);
+      run += total << 16;   // every low-half digit (d < lanes) precedes every high-half digit
+      for (uint32_t i = 0; i < lanes; ++i) {
+        const uint32_t a = rs_pad(w0 + i);
+        const uint32_t w = rs_cnt[a];
+        rs_cnt[a] = run;
+        run += w;
       }
     }
     __syncthreads();
+    // position inside the digit-sorted tile; per-digit start of the tile -> global destination base
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
-      const uint32_t pos = k * RS_THREADS + tid;
-      if (pos < tile_n) {
-        const uint32_t kk = sm.keys[pos];
-        const uint32_t dst = sm.out_base[(kk >> shift) & mask] + pos;
-        keys_out[dst] = kk;
-        vals_out[dst] = sm.vals[pos];
+      const unsigned short *c = reinterpret_cast<const unsigned short *>(
+          cbytes + rs_counter_off((key[k] >> shift) & mask, lanes_mask, lanes_log, tid));
+      pos[k] += *c;
+    }
+    if (tid <= mask) {
+      const uint32_t tstart = *reinterpret_cast<const unsigned short *>(
+          cbytes + rs_counter_off(tid, lanes_mask, lanes_log, 0));
+      tail.out_base[tid] = dbase + block_hist[(size_t)tid * stride + t] - tstart;
+    }
+    __syncthreads();   // counters are dead: the same memory now stages the sorted tile
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) stage[pos[k]] = make_uint2(key[k], val[k]);
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+      const uint32_t q = k * RS_THREADS + tid;
+      if (q < tile_n) {
+        const uint2 kv = stage[q];
+        const uint32_t dst = tail.out_base[(kv.x >> shift) & mask] + q;
+        keys_out[dst] = kv.x;
+        vals_out[dst] = kv.y;
       }
     }
     __syncthreads();
@@ -228,7 +294,7 @@ rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restri
 
 void sort_plan(int nbits, int &passes, int &bits_per_pass) {
   if (nbits < 1) nbits = 1;
-  passes = (nbits + 7) / 8;
+  passes = (nbits + RS_MAX_BITS - 1) / RS_MAX_BITS;
   bits_per_pass = (nbits + passes - 1) / passes;
 }
 
@@ -236,7 +302,10 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
                       bool identity_vals, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(rs_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem));
+    cudaFuncSetAttribute(rs_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)rs_scatter_smem(RS_MAX_BITS));
+    cudaFuncSetAttribute(rs_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)rs_counter_words(RS_MAX_BITS) * 4);
     attr_set = true;
   }
   if (n_upper > sb.capacity) n_upper = sb.capacity;
@@ -249,14 +318,14 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
   for (int p = 0; p < passes; ++p) {
     const int shift = begin_bit + p * bpp;
     const int bits = (end_bit - shift) < bpp ? (end_bit - shift) : bpp;
-    const uint32_t mask = (1u << bits) - 1u;
+    const size_t smem = rs_scatter_smem(bits);
     g_launches += 3;
-    rs_hist_kernel<<<grid, RS_THREADS, 0, st>>>(sb.keys[cur], d_n, sb.capacity, shift, mask, sb.block_hist,
-                                               sb.max_tiles);
-    rs_scan_kernel<<<mask + 1, 256, 0, st>>>(sb.block_hist, sb.max_tiles, d_n, sb.capacity, sb.digit_totals);
-    rs_scatter_kernel<<<grid, RS_THREADS, sizeof(RsSmem), st>>>(
+    rs_hist_kernel<<<grid, RS_THREADS, rs_counter_words(bits) * 4, st>>>(sb.keys[cur], d_n, sb.capacity, shift, bits,
+                                                                      sb.block_hist, sb.max_tiles);
+    rs_scan_kernel<<<1u << bits, 256, 0, st>>>(sb.block_hist, sb.max_tiles, d_n, sb.capacity, sb.digit_totals);
+    rs_scatter_kernel<<<grid, RS_THREADS, smem, st>>>(
         sb.keys[cur], (p == 0 && identity_vals) ? nullptr : sb.vals[cur], sb.keys[cur ^ 1], sb.vals[cur ^ 1], d_n,
-        sb.capacity, shift, mask, sb.block_hist, sb.max_tiles, sb.digit_totals);
+        sb.capacity, shift, bits, (uint32_t)(smem - sizeof(RsTail)), sb.block_hist, sb.max_tiles, sb.digit_totals);
     cur ^= 1;
   }
   return cur;
