@@ -39,13 +39,17 @@ constexpr int RS_WARPS = RS_THREADS / 32;
 // thread" into the element's stable position inside the tile.  Two digits share a 32-bit word
 // (digit d and d + LANES, LANES = radix / 2), so the scan adds whole words: no half can overflow
 // because a tile has 4096 < 65536 elements.  Word (lane, thread) lives at PAD(lane * 256 + thread);
-// the padding (one word per 32) keeps both the per-thread bumps and the raking segments
-// bank-conflict free.
-__device__ __forceinline__ uint32_t rs_pad(uint32_t i) { return i + (i >> 5); }
-constexpr uint32_t rs_counter_words(int bits) {
-  const uint32_t w = (uint32_t)RS_THREADS << (bits > 1 ? bits - 1 : 0);
-  return w + (w >> 5);
-}
+// the padding (two words per 32) keeps the per-thread bumps and the 64-bit raking loads
+// bank-conflict free and 8-byte aligned.
+__host__ __device__ constexpr uint32_t rs_pad(uint32_t i) { return i + ((i >> 5) << 1); }
+template <int BITS> struct RsGeom {
+  static constexpr int LANES_LOG = BITS > 1 ? BITS - 1 : 0;
+  static constexpr uint32_t LANES = 1u << LANES_LOG;          // counter words per thread
+  static constexpr uint32_t MASK = (1u << BITS) - 1u;
+  static constexpr uint32_t WORDS = rs_pad(LANES * RS_THREADS);
+  static constexpr uint32_t LANE_STRIDE = rs_pad(RS_THREADS) * 4u;   // bytes between counter lanes
+};
+__host__ __device__ constexpr uint32_t rs_counter_words(int bits) { return rs_pad((uint32_t)RS_THREADS << (bits > 1 ? bits - 1 : 0)); }
 
 // exclusive scan of one value per thread over the 256-thread CTA; *total = sum (all threads)
 __device__ __forceinline__ uint32_t cta_excl_scan256(uint32_t v, uint32_t *wt, uint32_t lane, uint32_t warp,
@@ -92,31 +96,54 @@ __device__ __forceinline__ void rs_load_blocked(const uint32_t *__restrict__ src
   }
 }
 
-// byte offset of the 16-bit counter of digit d for this thread
-__device__ __forceinline__ uint32_t rs_counter_off(uint32_t d, uint32_t lanes_mask, int lanes_log, uint32_t tid) {
-  const uint32_t lane = d & lanes_mask, sub = d >> lanes_log;
-  return rs_pad(lane * RS_THREADS + tid) * 4u + sub * 2u;
+// byte offset of the 16-bit counter of digit d for the thread whose padded byte offset is tid_off
+template <int BITS>
+__device__ __forceinline__ uint32_t rs_counter_off(uint32_t d, uint32_t tid_off) {
+  using G = RsGeom<BITS>;
+  return (d & (G::LANES - 1u)) * G::LANE_STRIDE + (d >> G::LANES_LOG) * 2u + tid_off;
+}
+
+// Sum (SCAN = false) or in-place exclusive scan seeded with `run` (SCAN = true) of the COUNT
+// consecutive counter words starting at word index w0 (w0 a multiple of COUNT or of 32).
+template <uint32_t COUNT, bool SCAN>
+__device__ __forceinline__ uint32_t rs_rake(uint32_t *cnt, uint32_t w0, uint32_t run) {
+  if constexpr (COUNT == 1) {
+    const uint32_t a = rs_pad(w0), w = cnt[a];
+    if (SCAN) cnt[a] = run;
+    return run + w;
+  } else {
+#pragma unroll
+    for (uint32_t seg = 0; seg < COUNT; seg += 32) {
+      uint2 *p = reinterpret_cast<uint2 *>(cnt + rs_pad(w0 + seg));
+      constexpr uint32_t PAIRS = (COUNT < 32 ? COUNT : 32) / 2;
+#pragma unroll
+      for (uint32_t q = 0; q < PAIRS; ++q) {
+        const uint2 w = p[q];
+        if (SCAN) p[q] = make_uint2(run, run + w.x);
+        run += w.x + w.y;
+      }
+    }
+    return run;
+  }
 }
 
 // ---- digit histogram of every tile -----------------------------------------------------------
+template <int BITS>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ d_n, uint32_t cap, int shift,
-               int bits, uint32_t *__restrict__ block_hist, uint32_t stride) {
+               uint32_t *__restrict__ block_hist, uint32_t stride) {
+  using G = RsGeom<BITS>;
   extern __shared__ __align__(16) uint32_t rs_cnt[];
   const uint32_t n = num_elems(d_n, cap);
   const uint32_t ntiles = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
   const uint32_t tid = threadIdx.x;
-  const uint32_t mask = (1u << bits) - 1u;
-  const int lanes_log = bits > 1 ? bits - 1 : 0;
-  const uint32_t lanes = 1u << lanes_log, lanes_mask = lanes - 1u;
-  const uint32_t words = rs_pad(lanes * RS_THREADS);
-  // reduction mapping: thread = (counter lane, part); each sums `span` threads' packed words
-  const uint32_t parts = lanes >= RS_THREADS ? 1u : RS_THREADS / lanes;   // power of two
-  const uint32_t span = RS_THREADS / parts;
-  const uint32_t r_lane = tid / parts, r_part = tid % parts;
+  const uint32_t tid_off = rs_pad(tid) * 4u;
+  // reduction mapping: thread = (counter lane, part); each sums SPAN threads' packed words
+  constexpr uint32_t PARTS = RS_THREADS / G::LANES, SPAN = G::LANES;   // PARTS * SPAN == RS_THREADS
+  const uint32_t r_lane = tid / PARTS, r_part = tid % PARTS;
   unsigned char *cbytes = reinterpret_cast<unsigned char *>(rs_cnt);
   for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-    for (uint32_t k = tid; k < words; k += RS_THREADS) rs_cnt[k] = 0;
+    for (uint32_t k = tid * 2; k < G::WORDS; k += RS_THREADS * 2) *reinterpret_cast<uint2 *>(rs_cnt + k) = make_uint2(0, 0);
     __syncthreads();
     uint32_t key[RS_ITEMS];
     const uint32_t first = t * RS_TILE + tid * RS_ITEMS;
@@ -125,25 +152,25 @@ rs_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ d
     for (int k = 0; k < RS_ITEMS; ++k) {
       if (first + k < n) {
         unsigned short *c = reinterpret_cast<unsigned short *>(
-            cbytes + rs_counter_off((key[k] >> shift) & mask, lanes_mask, lanes_log, tid));
+            cbytes + rs_counter_off<BITS>((key[k] >> shift) & G::MASK, tid_off));
         *c = *c + 1;
       }
     }
     __syncthreads();
-    uint32_t sum = 0;   // packed: low half = digit r_lane, high half = digit r_lane + lanes
-    if (r_lane < lanes)
-      for (uint32_t i = 0; i < span; ++i) sum += rs_cnt[rs_pad(r_lane * RS_THREADS + r_part * span + i)];
-    for (uint32_t o = 1; o < parts && o < 32; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (parts > 32) {   // only for 1- and 2-bit digits: finish across warps through shared memory
+    // packed sum: low half = digit r_lane, high half = digit r_lane + LANES
+    uint32_t sum = rs_rake<SPAN, false>(rs_cnt, r_lane * RS_THREADS + r_part * SPAN, 0u);
+#pragma unroll
+    for (uint32_t o = 1; o < PARTS && o < 32; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if constexpr (PARTS > 32) {   // narrow digits: finish across warps through shared memory
       __syncthreads();
       if ((tid & 31) == 0) rs_cnt[tid >> 5] = sum;
       __syncthreads();
       sum = 0;
-      if (r_part == 0) for (uint32_t w = 0; w < parts / 32; ++w) sum += rs_cnt[r_lane * (parts / 32) + w];
+      if (r_part == 0) for (uint32_t w = 0; w < PARTS / 32; ++w) sum += rs_cnt[r_lane * (PARTS / 32) + w];
     }
-    if (r_part == 0 && r_lane < lanes) {
+    if (r_part == 0) {
       block_hist[(size_t)r_lane * stride + t] = sum & 0xffffu;
-      if (bits > 0 && r_lane + lanes <= mask) block_hist[(size_t)(r_lane + lanes) * stride + t] = sum >> 16;
+      block_hist[(size_t)(r_lane + G::LANES) * stride + t] = sum >> 16;
     }
     __syncthreads();
   }
@@ -195,37 +222,36 @@ struct RsTail {
   uint32_t out_base[128];
   uint32_t wt[RS_WARPS + 1];
 };
-constexpr size_t rs_scatter_smem(int bits) {
+__host__ __device__ constexpr size_t rs_scatter_smem(int bits) {
   const size_t counters = (size_t)rs_counter_words(bits) * 4, staging = (size_t)RS_TILE * 8;
   return (counters > staging ? counters : staging) + sizeof(RsTail);
 }
 
+template <int BITS>
 __global__ void __launch_bounds__(RS_THREADS, 3)
 rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                   uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
-                  const uint32_t *__restrict__ d_n, uint32_t cap, int shift, int bits, uint32_t body_bytes,
+                  const uint32_t *__restrict__ d_n, uint32_t cap, int shift,
                   const uint32_t *__restrict__ block_hist, uint32_t stride,
                   const uint32_t *__restrict__ digit_totals) {
+  using G = RsGeom<BITS>;
   extern __shared__ __align__(16) uint32_t rs_cnt[];
   unsigned char *cbytes = reinterpret_cast<unsigned char *>(rs_cnt);
   uint2 *stage = reinterpret_cast<uint2 *>(rs_cnt);
-  RsTail &tail = *reinterpret_cast<RsTail *>(cbytes + body_bytes);
+  RsTail &tail = *reinterpret_cast<RsTail *>(cbytes + (rs_scatter_smem(BITS) - sizeof(RsTail)));
   const uint32_t n = num_elems(d_n, cap);
   const uint32_t ntiles = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t mask = (1u << bits) - 1u;
-  const int lanes_log = bits > 1 ? bits - 1 : 0;
-  const uint32_t lanes = 1u << lanes_log, lanes_mask = lanes - 1u;
-  const uint32_t words = rs_pad(lanes * RS_THREADS);
+  const uint32_t tid_off = rs_pad(tid) * 4u;
   // global base of digit `tid`: exclusive scan of the digit totals (same for every tile)
-  const uint32_t dt = tid <= mask ? digit_totals[tid] : 0;
+  const uint32_t dt = tid <= G::MASK ? digit_totals[tid] : 0;
   const uint32_t dbase = cta_excl_scan256(dt, tail.wt, lane, warp);
 
   for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const uint32_t tile_n = min((uint32_t)RS_TILE, n - t * RS_TILE);
-    for (uint32_t k = tid; k < words; k += RS_THREADS) rs_cnt[k] = 0;
-    __syncthreads();
-
+    for (uint32_t k = tid * 2; k < G::WORDS; k += RS_THREADS * 2) *reinterpret_cast<uint2 *>(rs_cnt + k) = make_uint2(0, 0);
+    // this tile's per-digit offset among all tiles (independent of the ranking: fetch it early)
+    const uint32_t tile_digit_off = tid <= G::MASK ? block_hist[(size_t)tid * stride + t] : 0;
     uint32_t key[RS_ITEMS], val[RS_ITEMS], pos[RS_ITEMS];
     const uint32_t first = t * RS_TILE + tid * RS_ITEMS;
     rs_load_blocked(keys_in, first, n, 0xffffffffu, key);
@@ -234,11 +260,12 @@ rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restri
 #pragma unroll
       for (int k = 0; k < RS_ITEMS; ++k) val[k] = first + k;
     }
+    __syncthreads();
     // count: pos[k] = how many earlier elements of THIS thread have the same digit
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
       unsigned short *c = reinterpret_cast<unsigned short *>(
-          cbytes + rs_counter_off((key[k] >> shift) & mask, lanes_mask, lanes_log, tid));
+          cbytes + rs_counter_off<BITS>((key[k] >> shift) & G::MASK, tid_off));
       const uint32_t r = *c;
       *c = (unsigned short)(r + 1);
       pos[k] = r;
@@ -246,33 +273,25 @@ rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restri
     __syncthreads();
 
     // raking scan over all counter words in (counter lane, thread) order: thread `tid` owns the
-    // `lanes` consecutive words starting at tid * lanes
+    // LANES consecutive words starting at tid * LANES
     {
-      const uint32_t w0 = tid * lanes;
-      uint32_t sum = 0;
-      for (uint32_t i = 0; i < lanes; ++i) sum += rs_cnt[rs_pad(w0 + i)];
+      const uint32_t sum = rs_rake<G::LANES, false>(rs_cnt, tid * G::LANES, 0u);
       uint32_t total;
       uint32_t run = cta_excl_scan256(sum, tail.wt, lane, warp, &total);
-      run += total << 16;   // every low-half digit (d < lanes) precedes every high-half digit
-      for (uint32_t i = 0; i < lanes; ++i) {
-        const uint32_t a = rs_pad(w0 + i);
-        const uint32_t w = rs_cnt[a];
-        rs_cnt[a] = run;
-        run += w;
-      }
+      run += total << 16;   // every low-half digit (d < LANES) precedes every high-half digit
+      rs_rake<G::LANES, true>(rs_cnt, tid * G::LANES, run);
     }
     __syncthreads();
     // position inside the digit-sorted tile; per-digit start of the tile -> global destination base
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
       const unsigned short *c = reinterpret_cast<const unsigned short *>(
-          cbytes + rs_counter_off((key[k] >> shift) & mask, lanes_mask, lanes_log, tid));
+          cbytes + rs_counter_off<BITS>((key[k] >> shift) & G::MASK, tid_off));
       pos[k] += *c;
     }
-    if (tid <= mask) {
-      const uint32_t tstart = *reinterpret_cast<const unsigned short *>(
-          cbytes + rs_counter_off(tid, lanes_mask, lanes_log, 0));
-      tail.out_base[tid] = dbase + block_hist[(size_t)tid * stride + t] - tstart;
+    if (tid <= G::MASK) {
+      const uint32_t tstart = *reinterpret_cast<const unsigned short *>(cbytes + rs_counter_off<BITS>(tid, 0u));
+      tail.out_base[tid] = dbase + tile_digit_off - tstart;
     }
     __syncthreads();   // counters are dead: the same memory now stages the sorted tile
 #pragma unroll
@@ -283,7 +302,7 @@ rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restri
       const uint32_t q = k * RS_THREADS + tid;
       if (q < tile_n) {
         const uint2 kv = stage[q];
-        const uint32_t dst = tail.out_base[(kv.x >> shift) & mask] + q;
+        const uint32_t dst = tail.out_base[(kv.x >> shift) & G::MASK] + q;
         keys_out[dst] = kv.x;
         vals_out[dst] = kv.y;
       }
@@ -298,16 +317,27 @@ void sort_plan(int nbits, int &passes, int &bits_per_pass) {
   bits_per_pass = (nbits + passes - 1) / passes;
 }
 
-int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,
-                      bool identity_vals, cudaStream_t st) {
+template <int BITS>
+static void launch_pass(SortBuffers &sb, int cur, bool identity, const uint32_t *d_n, int shift, uint32_t grid,
+                        cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(rs_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)rs_scatter_smem(RS_MAX_BITS));
-    cudaFuncSetAttribute(rs_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)rs_counter_words(RS_MAX_BITS) * 4);
+    cudaFuncSetAttribute(rs_scatter_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)rs_scatter_smem(BITS));
+    cudaFuncSetAttribute(rs_hist_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)rs_counter_words(BITS) * 4);
     attr_set = true;
   }
+  rs_hist_kernel<BITS><<<grid, RS_THREADS, rs_counter_words(BITS) * 4, st>>>(sb.keys[cur], d_n, sb.capacity, shift,
+                                                                            sb.block_hist, sb.max_tiles);
+  rs_scan_kernel<<<1u << BITS, 256, 0, st>>>(sb.block_hist, sb.max_tiles, d_n, sb.capacity, sb.digit_totals);
+  rs_scatter_kernel<BITS><<<grid, RS_THREADS, rs_scatter_smem(BITS), st>>>(
+      sb.keys[cur], identity ? nullptr : sb.vals[cur], sb.keys[cur ^ 1], sb.vals[cur ^ 1], d_n, sb.capacity, shift,
+      sb.block_hist, sb.max_tiles, sb.digit_totals);
+}
+
+int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,
+                      bool identity_vals, cudaStream_t st) {
   if (n_upper > sb.capacity) n_upper = sb.capacity;
   const uint32_t ntiles = (uint32_t)(((uint64_t)n_upper + RS_TILE - 1) / RS_TILE);
   int cur = 0;
@@ -318,14 +348,17 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
   for (int p = 0; p < passes; ++p) {
     const int shift = begin_bit + p * bpp;
     const int bits = (end_bit - shift) < bpp ? (end_bit - shift) : bpp;
-    const size_t smem = rs_scatter_smem(bits);
+    const bool ident = p == 0 && identity_vals;
     g_launches += 3;
-    rs_hist_kernel<<<grid, RS_THREADS, rs_counter_words(bits) * 4, st>>>(sb.keys[cur], d_n, sb.capacity, shift, bits,
-                                                                      sb.block_hist, sb.max_tiles);
-    rs_scan_kernel<<<1u << bits, 256, 0, st>>>(sb.block_hist, sb.max_tiles, d_n, sb.capacity, sb.digit_totals);
-    rs_scatter_kernel<<<grid, RS_THREADS, smem, st>>>(
-        sb.keys[cur], (p == 0 && identity_vals) ? nullptr : sb.vals[cur], sb.keys[cur ^ 1], sb.vals[cur ^ 1], d_n,
-        sb.capacity, shift, bits, (uint32_t)(smem - sizeof(RsTail)), sb.block_hist, sb.max_tiles, sb.digit_totals);
+    switch (bits) {
+      case 1: launch_pass<1>(sb, cur, ident, d_n, shift, grid, st); break;
+      case 2: launch_pass<2>(sb, cur, ident, d_n, shift, grid, st); break;
+      case 3: launch_pass<3>(sb, cur, ident, d_n, shift, grid, st); break;
+      case 4: launch_pass<4>(sb, cur, ident, d_n, shift, grid, st); break;
+      case 5: launch_pass<5>(sb, cur, ident, d_n, shift, grid, st); break;
+      case 6: launch_pass<6>(sb, cur, ident, d_n, shift, grid, st); break;
+      default: launch_pass<7>(sb, cur, ident, d_n, shift, grid, st); break;
+    }
     cur ^= 1;
   }
   return cur;
