@@ -173,13 +173,13 @@ def stage_rooflines(tm, st, pairs, blended, W, H, tiles, clocks_mhz, peaks):
     """Per-stage achieved vs roofline from ALGORITHMIC bytes / flops."""
     N, V, D = st.num_gaussians, st.num_drawn, st.num_duplicates
     tile_bits = st.key_bits - 32
-    pb = (tile_bits + 7) // 8                              # digits of sort B (sort A: 4 digits of 8 bits)
+    pb = (tile_bits + 6) // 7                              # digits of sort B (sort A: 5 digits of 7/6 bits)
     hbm = peaks["hbm_gbs"]
     mhz = clocks_mhz or peaks.get("sm_max_mhz", 1965.0)
     fp32_peak = 2 * 128 * 148 * mhz * 1e6 / 1e12          # TFLOP/s at the observed SM clock
     # per digit: 4 B histogram read + 8 B read + 8 B write per element (first digit of sort A
     # generates its values: 4 B less)
-    alg_bytes = {"k1_project": 56 * N + 48 * V + 4 * N, "k3a_sort_depth": (4 * 20 - 4) * N,
+    alg_bytes = {"k1_project": 56 * N + 48 * V + 4 * N, "k3a_sort_depth": (5 * 20 - 4) * N,
                  "k2_duplicate": 8 * N + 16 * V + 8 * D, "k3b_sort_tile": 20 * pb * D,
                  "k4_ranges": 4 * D + 8 * tiles}
     out = {}

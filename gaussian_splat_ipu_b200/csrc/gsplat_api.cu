@@ -303,6 +303,17 @@ int gsplat_set_camera(gsplat_ctx *ctx, const float mv[16], const float proj[16],
   return GSPLAT_OK;
 }
 
+int gsplat_set_band(gsplat_ctx *ctx, int row_begin, int row_end) {
+  if (!ctx) return GSPLAT_E_ARG;
+  if (row_begin < 0 || row_end > ctx->tiles_down || row_begin > row_end)
+    return fail(ctx, GSPLAT_E_ARG, "gsplat_set_band: bad tile-row band");
+  ctx->cfg.band_row_begin = row_begin;
+  ctx->cfg.band_row_end = row_end;
+  ctx->fp.row_begin = row_begin;
+  ctx->fp.row_end = row_end;
+  return GSPLAT_OK;
+}
+
 }  // extern "C"
 
 #include "gsplat_api_frame.inc"

@@ -52,6 +52,7 @@ SYMBOLS = {
     "gsplat_last_error": (C.c_char_p, [_vp]),
     "gsplat_upload_scene": (C.c_int, [_vp, _fp, C.c_size_t]),
     "gsplat_set_camera": (C.c_int, [_vp, _fp, _fp, C.c_float, C.c_float]),
+    "gsplat_set_band": (C.c_int, [_vp, C.c_int, C.c_int]),
     "gsplat_render": (C.c_int, [_vp]),
     "gsplat_sync": (C.c_int, [_vp]),
     "gsplat_read_framebuffer_tiled_f32": (C.c_int, [_vp, _vp]),
@@ -205,6 +206,10 @@ class B200Splatter:
 
     def updateFocalLengths(self, fx, fy):
         self._fxy = (float(fx), float(fy))
+
+    def set_band(self, row_begin, row_end):
+        """Tile-row band [row_begin, row_end) rendered from the next execute() on (multi-GPU bands)."""
+        self._check(self.lib.gsplat_set_band(self.h, int(row_begin), int(row_end)))
 
     def execute(self, sync=False):
         """One "project" program run (ipu_rasteriser.cpp:393-399,408-420); asynchronous."""

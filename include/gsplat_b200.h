@@ -79,6 +79,14 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *gaussians16, size_t n);
 int gsplat_set_camera(gsplat_ctx *ctx, const float modelview[16], const float projection[16],
                       float fov, float scale_div);
 
+/* Multi-GPU tile bands (the reference is single-IPU, src/main/splat.cpp:41-46): restrict
+ * this context to the tile rows [row_begin, row_end) from the next gsplat_render() on.  K1 still
+ * projects every Gaussian but clamps rectangles to the band, so K2-K5 only process the band's
+ * share of the duplicates; tiles outside the band keep count 0 and their framebuffer chunks are
+ * not written.  Band boundaries are host-side ints, re-chosen per frame from the previous frame's
+ * tile counts by the caller. */
+int gsplat_set_band(gsplat_ctx *ctx, int row_begin, int row_end);
+
 /* One run of the "project" program (ipu_rasteriser.cpp:393-399,408-420), converged
  * (SURVEY §8a): K1 project/cull, K3a radix sort of the Gaussians by depth, K2 duplicate (in depth
  * order), K3b stable radix sort of the duplicates by tile, K4 tile ranges, K5 blend.
