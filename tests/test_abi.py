@@ -107,3 +107,27 @@ def test_product_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cpp", ".h", ".hpp", ".inc", "Makefile")):
                 txt = open(os.path.join(dp, f), errors="replace").read()
                 assert "pyoracle" not in txt and "liboracle" not in txt and "splat_ref" not in txt, os.path.join(dp, f)
+
+
+def _build_shim_smoke(tmpdir):
+    import subprocess
+    exe = os.path.join(tmpdir, "shim_smoke")
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    libdir = os.path.dirname(sp.LIB_PATH)
+    cmd = [cxx, "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "cpp", "shim_smoke.cpp"), "-o", exe, "-L", libdir, "-lgsplat_b200",
+           f"-Wl,-rpath,{libdir}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+@pytest.mark.skipif(have_gpu(), reason="checks the no-GPU failure mode")
+def test_cpp_shim_compiles_and_fails_loudly_without_device(tmp_path):
+    """include/gsplat_b200.hpp (the IpuSplatter-shaped C++ host mirror) compiles warning-free,
+    links against the library, and without a device throws instead of falling back."""
+    import subprocess
+    sp.build_library()
+    exe = _build_shim_smoke(str(tmp_path))
+    r = subprocess.run([exe, "1000"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 3 and "no CPU fallback" in r.stdout, (r.returncode, r.stdout, r.stderr)
