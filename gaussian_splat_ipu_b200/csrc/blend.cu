@@ -61,7 +61,8 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   if (tid == 0) counts[tile] = n;
 
   const uint32_t tcol = tile % tiles_across, trow = tile / tiles_across;
-  const float xf = (float)(tcol * 32 + lane);
+  const float xf_first = (float)(tcol * 32);
+  const float xf = xf_first + (float)lane;
   const float ty0 = (float)(trow * tile_h);
   const float yf = ty0 + (float)row;
 
@@ -93,6 +94,20 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
           const float flo = ceilf(a.y - hy - ty0), fhi = floorf(a.y + hy - ty0);
           if (fhi < 0.f || flo > (float)(tile_h - 1)) { lo = 1; hi = 0; }
           else { lo = flo > 0.f ? (uint32_t)flo : 0u; hi = fhi < (float)(tile_h - 1) ? (uint32_t)fhi : (uint32_t)tile_h - 1; }
+          // Tighten to the rows the ellipse reaches INSIDE this tile's 32 columns: on row y the
+          // quadratic form is smallest at dx* = clamp(-B dy / A, [dx of last column, dx of first]);
+          // rows whose minimum already exceeds the bound (with margin) hold no pixel with
+          // alpha >= 1/255.  The set of passing rows is an interval (convexity): trim both ends.
+          const float bound = 2.0f * 0.6931472f * (L2 + 0.02f) * 1.001f + 1e-4f;
+          const float dxa = a.x - (xf_first + 31.0f), dxb = a.x - xf_first, invA = 1.0f / A;
+          auto reaches = [&](uint32_t rrow) {
+            const float dy = a.y - (ty0 + (float)rrow);
+            const float dx = fminf(fmaxf(-B * dy * invA, dxa), dxb);
+            return A * dx * dx + 2.0f * B * dx * dy + C * dy * dy <= bound;
+          };
+          while (lo <= hi && !reaches(lo)) ++lo;
+          while (hi > lo && !reaches(hi)) --hi;
+          if (lo > hi) { lo = 1; hi = 0; }
         }
       }
       sA[tid] = make_float4(a.x, a.y, -0.5f * LOG2E * A, -LOG2E * B);

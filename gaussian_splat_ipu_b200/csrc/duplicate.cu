@@ -62,14 +62,28 @@ __device__ __forceinline__ void st_relaxed(unsigned long long *p, unsigned long 
 
 // One CTA = one link of the chain = K2_CHUNK consecutive positions of the depth order
 // (K2_ITEMS per thread, striped so the loads coalesce and the rectangle gathers overlap).
+constexpr uint32_t K2_SMALL = 12;   // rectangles up to this many tiles are written by their own thread
 struct K2Smem {
-  uint32_t prefix[K2_CHUNK + 1];
-  uint32_t gauss[K2_CHUNK];
-  uint32_t cols[K2_CHUNK];   // c0 | width << 16
-  uint32_t row0[K2_CHUNK];
+  uint32_t prefix[K2_CHUNK];
   uint32_t wt[K2_THREADS / 32 + 1];
   uint32_t chain;            // this CTA's position in the chain, then its base offset
+  uint32_t n_big;
+  uint32_t big[K2_CHUNK];    // chunk entries with more than K2_SMALL tiles (usually none)
+  uint2 big_rect[K2_CHUNK];
+  uint32_t big_gauss[K2_CHUNK];
 };
+
+// writes the `cnt` (tile, gaussian) pairs q = first, first + step, ... of one rectangle
+__device__ __forceinline__ void emit_rect(uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t at,
+                                          uint2 rc, uint32_t g, int tiles_across, uint32_t first, uint32_t step,
+                                          uint32_t total) {
+  const uint32_t c0 = rc.x & 0xffffu, w = (rc.x >> 16) - c0 + 1, r0 = rc.y & 0xffffu;
+  for (uint32_t q = first; q < total; q += step) {
+    const uint32_t ty = r0 + q / w, tx = c0 + q % w;
+    keys[at + q] = ty * (uint32_t)tiles_across + tx;
+    vals[at + q] = g;
+  }
+}
 
 __global__ void __launch_bounds__(K2_THREADS)
 duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const uint32_t *__restrict__ sorted_gauss,
@@ -79,10 +93,12 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
   extern __shared__ __align__(16) unsigned char k2_smem_raw[];
   K2Smem &sm = *reinterpret_cast<K2Smem *>(k2_smem_raw);
   const uint32_t tid = threadIdx.x;
-  if (tid == 0) sm.chain = atomicAdd(ticket, 1u);
+  if (tid == 0) { sm.chain = atomicAdd(ticket, 1u); sm.n_big = 0; }
   __syncthreads();
   const uint32_t b = sm.chain;
   uint32_t g[K2_ITEMS];
+  uint2 rc[K2_ITEMS];
+  uint32_t cnt[K2_ITEMS];
   bool live[K2_ITEMS];
 #pragma unroll
   for (int i = 0; i < K2_ITEMS; ++i) {
@@ -92,17 +108,10 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
   }
 #pragma unroll
   for (int i = 0; i < K2_ITEMS; ++i) {
-    const uint32_t e = i * K2_THREADS + tid;
-    uint32_t t = 0, cols = 0, row0 = 0;
-    if (live[i]) {
-      const float4 c = __ldg(&p.rec[(size_t)g[i] * 3 + 2]);
-      const uint32_t cw = __float_as_uint(c.z), rw = __float_as_uint(c.w);
-      const uint32_t c0 = cw & 0xffffu, c1 = cw >> 16, r0 = rw & 0xffffu, r1 = rw >> 16;
-      cols = c0 | ((c1 - c0 + 1) << 16);
-      row0 = r0;
-      t = (c1 - c0 + 1) * (r1 - r0 + 1);
-    }
-    sm.prefix[e] = t; sm.gauss[e] = g[i]; sm.cols[e] = cols; sm.row0[e] = row0;
+    rc[i] = live[i] ? __ldg(&p.rect[g[i]]) : make_uint2(0u, 0u);
+    const uint32_t w = (rc[i].x >> 16) - (rc[i].x & 0xffffu) + 1, h = (rc[i].y >> 16) - (rc[i].y & 0xffffu) + 1;
+    cnt[i] = live[i] ? w * h : 0u;
+    sm.prefix[i * K2_THREADS + tid] = cnt[i];
   }
   __syncthreads();
   // exclusive scan of the chunk in position order: thread tid owns entries [tid*ITEMS, (tid+1)*ITEMS)
@@ -113,7 +122,6 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
   uint32_t ex = block_excl_scan<K2_THREADS>(sum, sm.wt, total);
 #pragma unroll
   for (int i = 0; i < K2_ITEMS; ++i) { sm.prefix[tid * K2_ITEMS + i] = ex; ex += loc[i]; }
-  if (tid == 0) sm.prefix[K2_CHUNK] = total;
 
   // ---- chained scan: publish the aggregate, look back for the exclusive prefix ------------------
   if (tid < 32) {
@@ -151,23 +159,34 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
   const uint32_t base = sm.chain;
   if (total == 0 || base == 0xffffffffu) return;
 
-  // The CTA's duplicates are the contiguous run [base, base + total): threads stride over it and
-  // find the owning Gaussian by binary search in the chunk prefix, so writes are coalesced and
-  // a Gaussian covering hundreds of tiles does not serialise one thread.
-  for (uint32_t k = tid; k < total; k += K2_THREADS) {
-    // largest i with prefix[i] <= k  (zero-count entries share their successor's prefix and are skipped)
-    uint32_t lo = 0, hi = K2_CHUNK;
+  // The CTA's duplicates are the contiguous run [base, base + total).  Neighbouring threads own
+  // neighbouring entries, so a warp's stores fall into one short contiguous span.  Small
+  // rectangles (the common case: 3.4 tiles on average) are written by their own thread; the rare
+  // large ones are queued and written by the whole CTA so they do not serialise one thread.
 #pragma unroll
-    for (int s = 0; s < K2_LOG_CHUNK; ++s) {
-      const uint32_t mid = (lo + hi) >> 1;
-      if (sm.prefix[mid] <= k) lo = mid; else hi = mid;
+  for (int i = 0; i < K2_ITEMS; ++i) {
+    if (cnt[i] == 0) continue;
+    const uint32_t e = i * K2_THREADS + tid;
+    if (cnt[i] <= K2_SMALL) {   // row-major walk of the rectangle without divisions
+      const uint32_t c0 = rc[i].x & 0xffffu, c1 = rc[i].x >> 16;
+      uint32_t at = base + sm.prefix[e], tx = c0, row = (rc[i].y & 0xffffu) * (uint32_t)tiles_across;
+      for (uint32_t q = 0; q < cnt[i]; ++q) {
+        keys[at] = row + tx;
+        vals[at] = g[i];
+        ++at;
+        if (tx == c1) { tx = c0; row += (uint32_t)tiles_across; } else { ++tx; }
+      }
+    } else {
+      const uint32_t slot = atomicAdd(&sm.n_big, 1u);
+      sm.big[slot] = e; sm.big_rect[slot] = rc[i]; sm.big_gauss[slot] = g[i];
     }
-    const uint32_t local = k - sm.prefix[lo];
-    const uint32_t cw = sm.cols[lo];
-    const uint32_t w = cw >> 16;
-    const uint32_t ty = sm.row0[lo] + local / w, tx = (cw & 0xffffu) + local % w;
-    keys[base + k] = ty * (uint32_t)tiles_across + tx;
-    vals[base + k] = sm.gauss[lo];
+  }
+  __syncthreads();
+  const uint32_t n_big = sm.n_big;
+  for (uint32_t s = 0; s < n_big; ++s) {
+    const uint2 r = sm.big_rect[s];
+    const uint32_t w = (r.x >> 16) - (r.x & 0xffffu) + 1, h = (r.y >> 16) - (r.y & 0xffffu) + 1;
+    emit_rect(keys, vals, base + sm.prefix[sm.big[s]], r, sm.big_gauss[s], tiles_across, tid, K2_THREADS, w * h);
   }
 }
 

@@ -144,7 +144,7 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   cudaSetDevice(ctx->cfg.device);
   if (ctx->st) cudaStreamSynchronize(ctx->st);
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
-  dfree(ctx->proj.rec);
+  dfree(ctx->proj.rec); dfree(ctx->proj.rect);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->d_scalars); dfree(ctx->lookback);
   free_sort(ctx->sort_a); free_sort(ctx->sort_b);
   dfree(ctx->ranges); dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
@@ -236,7 +236,7 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   CU(cudaStreamSynchronize(ctx->st));
   for (auto &sl : ctx->slots) sl.pending = false;
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
-  dfree(ctx->proj.rec); dfree(ctx->lookback);
+  dfree(ctx->proj.rec); dfree(ctx->proj.rect); dfree(ctx->lookback);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4);
   ctx->have_scene = ctx->have_frame = false;
   const size_t na = n ? n : 1;
@@ -247,6 +247,7 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   CU(cudaMalloc(&ctx->scene.s12, na * sizeof(float2)));
   CU(cudaMalloc(&ctx->proj.rec, na * 3 * sizeof(float4)));
   CU(cudaMemsetAsync(ctx->proj.rec, 0, na * 3 * sizeof(float4), ctx->st));
+  CU(cudaMalloc(&ctx->proj.rect, na * sizeof(uint2)));
   ctx->n_blocks = (uint32_t)((n + K2_CHUNK - 1) / K2_CHUNK);
   CU(cudaMalloc(&ctx->lookback, (ctx->n_blocks + 1) * sizeof(unsigned long long)));
   if (ctx->cfg.debug_records) {

@@ -41,6 +41,8 @@ struct SceneSoA {
 struct Projected {
   float4 *rec;
   uint32_t *depth_key;   // ~bits(clip z) for drawn Gaussians (z < 0  =>  key < 2^31)
+  uint2 *rect;           // {c0 | c1<<16, r0 | r1<<16} again, compact (8 B): K2 gathers it in depth
+                         // order, and a random 8 B read costs one 32 B sector instead of a 48 B record
 };
 constexpr uint32_t DEPTH_KEY_CULLED = 0xffffffffu;
 
@@ -83,8 +85,8 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
 // bit-reproducible.  Writes D to *total; sets *overflow (and writes nothing past the buffer) if
 // D > capacity.
 constexpr int K2_THREADS = 256;
-constexpr int K2_ITEMS = 8;
-constexpr int K2_LOG_CHUNK = 11;
+constexpr int K2_ITEMS = 4;
+constexpr int K2_LOG_CHUNK = 10;
 constexpr int K2_CHUNK = K2_THREADS * K2_ITEMS;   // Gaussians per CTA == per chain link
 static_assert((1 << K2_LOG_CHUNK) == K2_CHUNK, "binary search depth");
 void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t n,

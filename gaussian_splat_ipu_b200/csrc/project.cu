@@ -175,6 +175,7 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
           r[1] = make_float4(kz, kw, col.x, col.y);
           r[2] = make_float4(col.z, cz, __uint_as_float((uint32_t)c0 | ((uint32_t)c1 << 16)),
                              __uint_as_float((uint32_t)e0 | ((uint32_t)e1 << 16)));
+          out.rect[i] = make_uint2((uint32_t)c0 | ((uint32_t)c1 << 16), (uint32_t)e0 | ((uint32_t)e1 << 16));
         }
       }
     }
@@ -213,6 +214,7 @@ inject_kernel(const float *__restrict__ depth, const int32_t *__restrict__ rect4
         c.z = __uint_as_float((uint32_t)c0 | ((uint32_t)c1 << 16));
         c.w = __uint_as_float((uint32_t)e0 | ((uint32_t)e1 << 16));
         out.rec[(size_t)i * 3 + 2] = c;
+        out.rect[i] = make_uint2(__float_as_uint(c.z), __float_as_uint(c.w));
       }
     }
     out.depth_key[i] = touched ? ~__float_as_uint(z) : DEPTH_KEY_CULLED;

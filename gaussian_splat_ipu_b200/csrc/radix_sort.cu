@@ -365,15 +365,37 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
 }
 
 // ---- K4: per-tile ranges over the sorted tile keys (counts = end - start) -------
+// Each thread inspects four consecutive keys (one 128-bit load) plus the key before them: a range
+// starts where a key differs from its predecessor and ends where it differs from its successor.
 __global__ void __launch_bounds__(256)
 tile_ranges_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ d_n, uint32_t cap,
                    uint2 *__restrict__ ranges, uint32_t num_tiles) {
   const uint32_t n = num_elems(d_n, cap);
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t t = keys[i];
-    if (t >= num_tiles) continue;
-    if (i == 0 || keys[i - 1] != t) ranges[t].x = i;
-    if (i == n - 1 || keys[i + 1] != t) ranges[t].y = i + 1;
+  const uint32_t nquads = (n + 3) / 4;
+  for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < nquads; q += gridDim.x * blockDim.x) {
+    const uint32_t i0 = q * 4;
+    uint32_t k[4];
+    if (i0 + 4 <= n) {
+      const uint4 v = *reinterpret_cast<const uint4 *>(keys + i0);
+      k[0] = v.x; k[1] = v.y; k[2] = v.z; k[3] = v.w;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) k[e] = i0 + e < n ? keys[i0 + e] : 0xffffffffu;
+    }
+    uint32_t prev = i0 ? keys[i0 - 1] : 0xffffffffu;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const uint32_t i = i0 + e;
+      if (i < n && k[e] != prev) {
+        if (k[e] < num_tiles) ranges[k[e]].x = i;
+        if (i && prev < num_tiles) ranges[prev].y = i;
+      }
+      prev = k[e];
+    }
+    if (i0 + 4 >= n) {   // the thread holding the last element closes the last range
+      const uint32_t last = k[(n - 1) - i0];
+      if (last < num_tiles) ranges[last].y = n;
+    }
   }
 }
 
@@ -381,7 +403,7 @@ void launch_tile_ranges(const uint32_t *keys, const uint32_t *d_n, uint32_t n_up
                         uint32_t num_tiles, cudaStream_t st) {
   cudaMemsetAsync(ranges, 0, sizeof(uint2) * num_tiles, st);
   if (!n_upper) return;
-  const int blocks = min(ceil_div(n_upper, 256), 148 * 8);
+  const int blocks = min(ceil_div(n_upper, 1024), 148 * 8);
   ++g_launches;
   tile_ranges_kernel<<<blocks, 256, 0, st>>>(keys, d_n, cap, ranges, num_tiles);
 }
