@@ -126,12 +126,22 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
 
 
+def host_threads():
+    """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1: ignore it, the CPU
+    arm is meant to use the whole host)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_frame_time(kind, g, view, proj, W, H, threads=0):
     from oracle import pyoracle
     orc = pyoracle.Oracle(kind)
+    threads = threads or host_threads()
     t0 = time.perf_counter()
     f = orc.frame(g, view, proj, FOV, SCALE_DIV, W, H, render=True, threads=threads)
-    return time.perf_counter() - t0, orc.cores, f
+    return time.perf_counter() - t0, threads, f
 
 
 def reference_arm(args):
@@ -317,6 +327,73 @@ def gpu_arm(args):
         dist.destroy_process_group()
 
 
+def bands_arm(args):
+    """Secondary mode (BASELINE configs[3]): ONE frame per step split into tile-row
+    bands over the N GPUs ("strong" scaling).  Every rank projects the whole replicated scene but
+    bins/sorts/blends only its band; band cuts are re-balanced every frame from the previous
+    frame's per-tile counts; BGR8 bands are gathered to rank 0 over NCCL point-to-point ops."""
+    import torch
+    from gaussian_splat_ipu_b200.splatter import B200Splatter
+    from gaussian_splat_ipu_b200 import sharding as sh
+    rank, world, local = dist_env()
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    g, base, proj, W, H = make_scene(args.workload)
+    s = B200Splatter(g, W, H, device=local)
+    s.updateProjection(proj)
+    s.updateFocalLengths(FOV, SCALE_DIV)
+    views = [view_for(base, k) for k in range(ORBIT_VIEWS)]
+    bgr_ptr, _ = s.device_pointers()
+    image = torch.as_tensor(sh.DeviceArray(bgr_ptr, (H * W * 3,), "|u1"), device=f"cuda:{local}")
+    counts_dev = torch.zeros(s.num_tiles, dtype=torch.int32, device=f"cuda:{local}")
+    cuts = [round(s.tiles_down * i / world) for i in range(world + 1)]
+    imb = []
+
+    def step(k):
+        nonlocal cuts
+        s.updateModelView(views[k % ORBIT_VIEWS])
+        s.set_band(cuts[rank], cuts[rank + 1])
+        s.execute()
+        s.postprocess_bgr8()
+        counts = s.getIPUHistogram()                     # waits for the frame; this rank's band only
+        if dist is not None:
+            counts_dev.copy_(torch.from_numpy(counts.astype(np.int32)))
+            sh.gather_bands(image, cuts, s.tile_h, W, 3, dst=0)
+            sh.allgather_tile_counts(counts_dev)
+            counts = counts_dev.cpu().numpy()
+        cost = sh.row_costs(counts, s.tiles_across, s.tile_w * s.tile_h)
+        imb.append(sh.band_imbalance(cost, cuts))
+        cuts = sh.balance_bands(cost, world)             # for the NEXT frame
+
+    for k in range(args.warmup):
+        step(k)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step(args.warmup + k)
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    fps = args.steps / float(dt.item())
+    if rank == 0:
+        chk = int(image[::97].to(torch.int64).sum().item())
+        print(json.dumps({"metric": "frames_per_second", "mode": "tile-row bands of one frame", "value": fps,
+                          "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                          "ms_per_step": 1e3 / fps, "higher_is_better": True, "scaling": "strong", "dtype": "f32",
+                          "data": "synthetic", "config": {"workload": args.workload, "width": W, "height": H,
+                                                          "gaussians": int(g.shape[0])},
+                          "band_imbalance_mean": float(np.mean(imb[args.warmup:])), "last_cuts": cuts,
+                          "gathered_bytes_per_step": W * H * 3, "checksum": chk}), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -324,11 +401,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--mode", default="views", choices=["views", "bands"],
+                    help="views (default, the headline): one whole view per GPU per step; bands: one frame per "
+                         "step split into tile-row bands over the GPUs, gathered to rank 0")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stage-report", default=None, help="write the per-stage roofline table (JSON) to this path")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
+    elif args.mode == "bands":
+        bands_arm(args)
     else:
         gpu_arm(args)
 
