@@ -27,8 +27,19 @@ struct FrameSlot {
   cudaEvent_t ev[EV_COUNT]{};
   cudaEvent_t done = nullptr;
   uint32_t *h = nullptr;   // pinned: [0] D  [1] V  [2] overflow
-  bool pending = false, timed = false;
+  bool pending = false, timed = false, overflowed = false;
   uint64_t frame_no = 0;
+};
+
+// One slot of the double-buffered frame stream (gsplat_render_streamed / gsplat_acquire_frame):
+// device staging written on the render stream, pinned host copies filled on the copy stream.
+struct StreamSlot {
+  uint8_t *d_bgr = nullptr, *h_bgr = nullptr;
+  uint32_t *d_counts = nullptr, *h_counts = nullptr;
+  cudaEvent_t rendered = nullptr, copied = nullptr;
+  uint64_t ticket = 0, frame_no = 0;
+  bool used = false;
+  FrameParams fp{};
 };
 
 // device scalars
@@ -67,6 +78,10 @@ struct gsplat_ctx {
   size_t need_grow = 0;       // largest D seen by an overflowed frame
   cudaEvent_t t0 = nullptr, t1 = nullptr, post0 = nullptr, post1 = nullptr;
   bool post_pending = false;
+  // frame stream (allocated on first use)
+  cudaStream_t copy_st = nullptr;
+  StreamSlot sslots[GSPLAT_STREAM_SLOTS];
+  uint64_t next_ticket = 1;
   float last_ms[GSPLAT_NUM_TIMINGS] = {0};
   double acc_ms[GSPLAT_NUM_TIMINGS] = {0};
   uint64_t acc_frames = 0;
@@ -148,6 +163,15 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->d_scalars); dfree(ctx->lookback);
   free_sort(ctx->sort_a); free_sort(ctx->sort_b);
   dfree(ctx->ranges); dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
+  if (ctx->copy_st) cudaStreamSynchronize(ctx->copy_st);
+  for (auto &ss : ctx->sslots) {
+    dfree(ss.d_bgr); dfree(ss.d_counts);
+    if (ss.h_bgr) cudaFreeHost(ss.h_bgr);
+    if (ss.h_counts) cudaFreeHost(ss.h_counts);
+    if (ss.rendered) cudaEventDestroy(ss.rendered);
+    if (ss.copied) cudaEventDestroy(ss.copied);
+  }
+  if (ctx->copy_st) cudaStreamDestroy(ctx->copy_st);
   if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
   for (auto &sl : ctx->slots) {
     for (auto &e : sl.ev) if (e) cudaEventDestroy(e);
@@ -312,6 +336,9 @@ int gsplat_set_band(gsplat_ctx *ctx, int row_begin, int row_end) {
   ctx->cfg.band_row_end = row_end;
   ctx->fp.row_begin = row_begin;
   ctx->fp.row_end = row_end;
+  // tiles that leave the band must read count 0 (K5 only writes the counts of the tiles it renders)
+  CU(cudaSetDevice(ctx->cfg.device));
+  CU(cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * ctx->num_tiles, ctx->st));
   return GSPLAT_OK;
 }
 

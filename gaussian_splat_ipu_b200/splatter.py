@@ -55,6 +55,8 @@ SYMBOLS = {
     "gsplat_set_band": (C.c_int, [_vp, C.c_int, C.c_int]),
     "gsplat_render": (C.c_int, [_vp]),
     "gsplat_sync": (C.c_int, [_vp]),
+    "gsplat_render_streamed": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "gsplat_acquire_frame": (C.c_int, [_vp, C.c_uint64, C.POINTER(_vp), C.POINTER(_vp)]),
     "gsplat_read_framebuffer_tiled_f32": (C.c_int, [_vp, _vp]),
     "gsplat_read_framebuffer_bgr8": (C.c_int, [_vp, _vp, C.c_size_t]),
     "gsplat_read_tile_counts": (C.c_int, [_vp, _vp]),
@@ -221,6 +223,25 @@ class B200Splatter:
 
     def sync(self):
         self._check(self.lib.gsplat_sync(self.h))
+
+    def executeStreamed(self) -> int:
+        """execute() whose BGR8 frame and tile counts are copied to a pinned host slot in the
+        background (the render loop's imagePtr/imagePtrBuffered swap, src/main/splat.cpp:281-283).
+        Returns the frame's ticket for acquireFrame()."""
+        self._check(self.lib.gsplat_set_camera(self.h, self._mv.ctypes.data_as(_fp), self._proj.ctypes.data_as(_fp),
+                                               self._fxy[0], self._fxy[1]))
+        t = C.c_uint64()
+        self._check(self.lib.gsplat_render_streamed(self.h, C.byref(t)))
+        return int(t.value)
+
+    def acquireFrame(self, ticket: int):
+        """Waits for a streamed frame; returns ((H, W, 3) BGR8, (num_tiles,) counts) as views of the
+        context's pinned slot, valid until the second-next executeStreamed()."""
+        b, c = _vp(), _vp()
+        self._check(self.lib.gsplat_acquire_frame(self.h, ticket, C.byref(b), C.byref(c)))
+        img = np.frombuffer((C.c_uint8 * (self.height * self.width * 3)).from_address(b.value), np.uint8)
+        cnt = np.frombuffer((C.c_uint32 * self.num_tiles).from_address(c.value), np.uint32)
+        return img.reshape(self.height, self.width, 3), cnt
 
     def getFrameBuffer(self, out: np.ndarray | None = None) -> np.ndarray:
         """(H, W, 3) BGR8 image, ipu_rasteriser.cpp:131-144."""

@@ -108,6 +108,27 @@ int gsplat_read_framebuffer_bgr8(gsplat_ctx *ctx, uint8_t *dst, size_t pitch);
  * (tiles outside the band are 0). */
 int gsplat_read_tile_counts(gsplat_ctx *ctx, uint32_t *dst);
 
+/* ---- double-buffered frame stream ---------------------------------------------------------------
+ * The render loop of the reference renders into one cv::Mat while its AsyncTask thread encodes /
+ * sends the previous one, then swaps them (src/main/splat.cpp:215-226,281-283: imagePtr /
+ * imagePtrBuffered).  The same two-deep pipeline, with the device-to-host copy inside it:
+ *
+ *   gsplat_render_streamed   gsplat_render() + the BGR8 post-process, then an asynchronous copy of
+ *                            the BGR8 image and the per-tile counts into one of the context's
+ *                            GSPLAT_STREAM_SLOTS pinned host slots on a second (copy) stream.
+ *                            Returns at once with a ticket; frame k+1 renders while frame k's
+ *                            pixels cross PCIe.
+ *   gsplat_acquire_frame     waits for that ticket's copy and hands out pointers INTO the pinned
+ *                            slot: *bgr8 = height rows of 3*width bytes (getFrameBuffer's image),
+ *                            *counts = tiles_across*tiles_down values (getIPUHistogram).  Either may
+ *                            be NULL.  The pointers stay valid until the second-next
+ *                            gsplat_render_streamed (the slot is then re-used); a ticket older than
+ *                            that fails with GSPLAT_E_STATE.  A frame that overflowed the duplicate
+ *                            buffer is re-run here (same camera) before the call returns.          */
+#define GSPLAT_STREAM_SLOTS 2
+int gsplat_render_streamed(gsplat_ctx *ctx, uint64_t *ticket);
+int gsplat_acquire_frame(gsplat_ctx *ctx, uint64_t ticket, const uint8_t **bgr8, const uint32_t **counts);
+
 typedef struct gsplat_frame_stats {
   uint64_t num_gaussians; /* N                                             */
   uint64_t num_drawn;     /* V: Gaussians passing the render predicate      */

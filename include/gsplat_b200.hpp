@@ -99,6 +99,20 @@ public:
     check(gsplat_read_tile_counts(ctx_, counts.data()));
   }
 
+  // Two-deep frame stream: the render loop's imagePtr / imagePtrBuffered swap
+  // (src/main/splat.cpp:215-226,281-283) with the device-to-host copy inside the pipeline.
+  // executeStreamed() returns a ticket at once; acquireFrame(ticket, ...) waits for that frame and
+  // points into pinned host memory that stays valid until the second-next executeStreamed().
+  std::uint64_t executeStreamed() {
+    check(gsplat_set_camera(ctx_, modelView_, projection_, fov_, scaleDiv_));
+    std::uint64_t t = 0;
+    check(gsplat_render_streamed(ctx_, &t));
+    return t;
+  }
+  void acquireFrame(std::uint64_t ticket, const std::uint8_t **bgr, const std::uint32_t **counts = nullptr) {
+    check(gsplat_acquire_frame(ctx_, ticket, bgr, counts));
+  }
+
   // multi-GPU tile bands (no reference equivalent: single IPU, src/main/splat.cpp:41-46)
   void setBand(int rowBegin, int rowEnd) { check(gsplat_set_band(ctx_, rowBegin, rowEnd)); }
   gsplat_frame_stats stats() const {
