@@ -42,11 +42,17 @@ __device__ __forceinline__ float ex2_approx(float x) {
 //   sRows u16: row_lo | row_hi << 8 ; lo > hi: touches no row
 constexpr size_t BLEND_SMEM_PER_THREAD = 16 + 16 + 8 + 2;
 
-template <bool COUNT>
+//
+// Depth slices (see duplicate.cu): the list of a tile may arrive in several consecutive pieces, one
+// launch each.  Between launches a pixel's state lives in the framebuffer (C) and in `tstate`
+// (T, or -1 once the pixel has stopped); a tile whose pixels have all stopped raises
+// tile_done[tile] so that later slices neither emit duplicates for it nor launch work on it.
+// FIRST: start from T = 1, C = 0.  LAST: no state is saved.
+template <bool COUNT, bool FIRST, bool LAST>
 __global__ void __launch_bounds__(BLEND_MAX_ROWS * 32)
 blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
-             int tiles_across, int row_begin, int tile_h, float4 *__restrict__ fb,
-             uint32_t *__restrict__ counts, unsigned long long *__restrict__ pair_counters) {
+             int tiles_across, int row_begin, int full_tile_h, int tile_h, float4 *__restrict__ fb,
+             float *__restrict__ tstate, TileState ts, unsigned long long *__restrict__ pair_counters) {
   extern __shared__ __align__(16) unsigned char blend_smem_raw[];
   const long long t_begin = COUNT ? clock64() : 0;
   const uint32_t tid = threadIdx.x, lane = tid & 31, row = tid >> 5;
@@ -55,20 +61,32 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   float4 *sB = sA + nthreads;
   float2 *sC = reinterpret_cast<float2 *>(sB + nthreads);
   uint16_t *sRows = reinterpret_cast<uint16_t *>(sC + nthreads);
-  const uint32_t tile = blockIdx.x + (uint32_t)row_begin * tiles_across;
+  // a CTA blends `tile_h` consecutive rows of a semantic tile (a "part": the whole tile, or 1/nsub
+  // of it so that a crowded tile's list is walked by several SMs at once); parts of one tile are
+  // neighbours in the grid
+  const uint32_t nsub = (uint32_t)(full_tile_h / tile_h), sub = blockIdx.x % nsub;
+  const uint32_t tile = blockIdx.x / nsub + (uint32_t)row_begin * tiles_across;
   const uint2 range = ranges[tile];
   const uint32_t n = range.y - range.x;
-  if (tid == 0) counts[tile] = n;
+  const uint32_t part = tile * nsub + sub;
+  if (!FIRST && (n == 0 || ts.part_done[part])) return;   // nothing new for this part: its state stands
+  const size_t px = (size_t)tile * (32 * full_tile_h) + (size_t)sub * (32 * tile_h) + tid;
 
   const uint32_t tcol = tile % tiles_across, trow = tile / tiles_across;
   const float xf_first = (float)(tcol * 32);
   const float xf = xf_first + (float)lane;
-  const float ty0 = (float)(trow * tile_h);
+  const float ty0 = (float)(trow * full_tile_h + sub * tile_h);
   const float yf = ty0 + (float)row;
 
   float T = 1.f, Cr = 0.f, Cg = 0.f, Cb = 0.f, Ca = 0.f;
   bool done = false;
-  uint32_t stop_at = n;            // COUNT: list entries this pixel visits (reference semantics)
+  if (!FIRST) {
+    const float4 c = fb[px];
+    Cr = c.x; Cg = c.y; Cb = c.z; Ca = c.w;
+    T = tstate[px];
+    done = T < 0.f;
+  }
+  uint32_t stop_at = done ? 0u : n;   // COUNT: list entries this pixel visits (reference semantics)
   unsigned long long n_blend = 0;  // COUNT
 
   for (uint32_t base = 0; base < n; base += nthreads) {
@@ -153,6 +171,13 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
     // all pixels of the tile stopped -> the rest of the list cannot contribute
     if (__syncthreads_and(done)) break;
   }
+  if (!LAST) {
+    tstate[px] = done ? -1.f : T;
+    if (__syncthreads_and(done) && tid == 0) {
+      ts.part_done[part] = 1;
+      if (atomicAdd(&ts.parts_done[tile], 1u) + 1u == nsub) ts.tile_done[tile] = 1;   // last part of the tile to stop
+    }
+  }
 
   if (COUNT) {
     unsigned long long n_visit = stop_at;
@@ -164,39 +189,45 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
     if (lane == 0) {
       atomicAdd(&pair_counters[0], n_visit); atomicAdd(&pair_counters[1], n_blend);
       atomicAdd(&pair_counters[2 + 2 * (size_t)tile + 1], n_visit);            // per-tile profile tap
-      atomicMax(&pair_counters[2 + 2 * (size_t)tile], (unsigned long long)(clock64() - t_begin));
+      atomicAdd(&pair_counters[2 + 2 * (size_t)tile], (unsigned long long)(clock64() - t_begin) / (unsigned)full_tile_h);
     }
   }
-  fb[(size_t)tile * (32 * tile_h) + tid] = make_float4(Cr, Cg, Cb, Ca);
+  fb[px] = make_float4(Cr, Cg, Cb, Ca);
 }
 
-template <bool COUNT>
+template <bool COUNT, bool FIRST, bool LAST>
 static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                           float4 *fb_tiled, uint32_t *counts, unsigned long long *pair_counters, cudaStream_t st) {
+                           float4 *fb_tiled, float *tstate, const TileState &ts, int split,
+                           unsigned long long *pair_counters, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(blend_kernel<COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaFuncSetAttribute(blend_kernel<COUNT, FIRST, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)(BLEND_MAX_ROWS * 32 * BLEND_SMEM_PER_THREAD));
     attr_set = true;
   }
   const int rows = fp.row_end - fp.row_begin;
   if (rows <= 0) return;
-  const int tile_h = (int)fp.tile_h;
-  // dynamic smem sized for this tile height so that 3 CTAs of a 32x20 tile fit per SM
+  const int full_h = (int)fp.tile_h;
+  const int tile_h = full_h / split;   // rows per CTA
+  // dynamic smem sized for this part height so that several CTAs fit per SM
   const size_t smem = (size_t)tile_h * 32 * BLEND_SMEM_PER_THREAD;
   ++g_launches;
-  blend_kernel<COUNT><<<rows * fp.tiles_across, tile_h * 32, smem, st>>>(
-      p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, tile_h, fb_tiled, counts, pair_counters);
+  blend_kernel<COUNT, FIRST, LAST><<<rows * fp.tiles_across * split, tile_h * 32, smem, st>>>(
+      p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, full_h, tile_h, fb_tiled, tstate, ts, pair_counters);
 }
 
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                  float4 *fb_tiled, uint32_t *counts, cudaStream_t st) {
-  launch_blend_t<false>(p, sorted_vals, ranges, fp, fb_tiled, counts, nullptr, st);
-}
-
-void launch_blend_count(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                        float4 *fb_tiled, uint32_t *counts, unsigned long long *pair_counters, cudaStream_t st) {
-  launch_blend_t<true>(p, sorted_vals, ranges, fp, fb_tiled, counts, pair_counters, st);
+                  float4 *fb_tiled, float *tstate, const TileState &ts, int split, bool first, bool last,
+                  unsigned long long *pair_counters, cudaStream_t st) {
+#define GSPLAT_BLEND(C, F, L) launch_blend_t<C, F, L>(p, sorted_vals, ranges, fp, fb_tiled, tstate, ts, split, pair_counters, st)
+  if (pair_counters) {
+    if (first) { if (last) GSPLAT_BLEND(true, true, true); else GSPLAT_BLEND(true, true, false); }
+    else { if (last) GSPLAT_BLEND(true, false, true); else GSPLAT_BLEND(true, false, false); }
+  } else {
+    if (first) { if (last) GSPLAT_BLEND(false, true, true); else GSPLAT_BLEND(false, true, false); }
+    else { if (last) GSPLAT_BLEND(false, false, true); else GSPLAT_BLEND(false, false, false); }
+  }
+#undef GSPLAT_BLEND
 }
 
 // ---- a10: IpuSplatter::getFrameBuffer, src/splat/ipu_rasteriser.cpp:115-144 -----------------

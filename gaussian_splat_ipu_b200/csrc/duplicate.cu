@@ -62,6 +62,15 @@ __device__ __forceinline__ void st_relaxed(unsigned long long *p, unsigned long 
 
 // One CTA = one link of the chain = K2_CHUNK consecutive positions of the depth order
 // (K2_ITEMS per thread, striped so the loads coalesce and the rectangle gathers overlap).
+//
+// Depth slices.  K5 stops a pixel at the first Gaussian that would push its transmittance under
+// 1e-4 (codelets.cpp:405-408); once every pixel of a tile has stopped, nothing further down the
+// tile's list can change the image.  The frame is therefore binned and blended in a few slices of
+// the depth order, nearest first: one launch covers positions [begin, end) of the depth order and,
+// when CHECK_DONE, emits nothing for tiles whose `tile_done` flag K5 raised in an earlier slice.
+// Every tile's list is then an exact PREFIX of the reference's list — complete unless the tile
+// saturated — and the framebuffer is bit-identical to the one-slice run.  The per-tile COUNTS of
+// the reference (codelets.cpp:501-504) still count every Gaussian: tile_count_kernel below.
 constexpr uint32_t K2_SMALL = 12;   // rectangles up to this many tiles are written by their own thread
 struct K2Smem {
   uint32_t prefix[K2_CHUNK];
@@ -73,22 +82,44 @@ struct K2Smem {
   uint32_t big_gauss[K2_CHUNK];
 };
 
-// writes the `cnt` (tile, gaussian) pairs q = first, first + step, ... of one rectangle
-__device__ __forceinline__ void emit_rect(uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t at,
-                                          uint2 rc, uint32_t g, int tiles_across, uint32_t first, uint32_t step,
-                                          uint32_t total) {
+template <bool CHECK_DONE>
+__device__ __forceinline__ bool tile_live(const uint8_t *__restrict__ tile_done, uint32_t tile) {
+  if (!CHECK_DONE) return true;
+  return __ldg(&tile_done[tile]) == 0;
+}
+
+// Writes the live tiles of one big rectangle, row-major, starting at `at`: one warp, 32 tiles per
+// step, positions from a ballot prefix (so skipped tiles leave no gap).
+template <bool CHECK_DONE>
+__device__ __forceinline__ void emit_rect_warp(uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t at,
+                                               uint2 rc, uint32_t g, int tiles_across,
+                                               const uint8_t *__restrict__ tile_done, uint32_t lane) {
   const uint32_t c0 = rc.x & 0xffffu, w = (rc.x >> 16) - c0 + 1, r0 = rc.y & 0xffffu;
-  for (uint32_t q = first; q < total; q += step) {
-    const uint32_t ty = r0 + q / w, tx = c0 + q % w;
-    keys[at + q] = ty * (uint32_t)tiles_across + tx;
-    vals[at + q] = g;
+  const uint32_t total = w * ((rc.y >> 16) - r0 + 1);
+  for (uint32_t q0 = 0; q0 < total; q0 += 32) {
+    const uint32_t q = q0 + lane;
+    uint32_t tile = 0;
+    bool live = false;
+    if (q < total) {
+      tile = (r0 + q / w) * (uint32_t)tiles_across + c0 + q % w;
+      live = tile_live<CHECK_DONE>(tile_done, tile);
+    }
+    const uint32_t m = __ballot_sync(0xffffffffu, live);
+    if (live) {
+      const uint32_t o = at + __popc(m & ((1u << lane) - 1u));
+      keys[o] = tile;
+      vals[o] = g;
+    }
+    at += __popc(m);
   }
 }
 
+template <bool CHECK_DONE>
 __global__ void __launch_bounds__(K2_THREADS)
 duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const uint32_t *__restrict__ sorted_gauss,
-                 uint32_t n, int tiles_across, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals,
-                 uint32_t capacity, unsigned long long *__restrict__ lookback, uint32_t *__restrict__ ticket,
+                 uint32_t begin, uint32_t end, int tiles_across, const uint8_t *__restrict__ tile_done,
+                 uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t capacity,
+                 unsigned long long *__restrict__ lookback, uint32_t *__restrict__ ticket,
                  uint32_t *__restrict__ total_out, uint32_t *__restrict__ overflow) {
   extern __shared__ __align__(16) unsigned char k2_smem_raw[];
   K2Smem &sm = *reinterpret_cast<K2Smem *>(k2_smem_raw);
@@ -102,16 +133,24 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
   bool live[K2_ITEMS];
 #pragma unroll
   for (int i = 0; i < K2_ITEMS; ++i) {
-    const uint32_t j = b * K2_CHUNK + i * K2_THREADS + tid;   // position in depth order
-    live[i] = j < n && sorted_keys[j] != DEPTH_KEY_CULLED;
+    const uint32_t j = begin + b * K2_CHUNK + i * K2_THREADS + tid;   // position in depth order
+    live[i] = j < end && sorted_keys[j] != DEPTH_KEY_CULLED;
     g[i] = live[i] ? sorted_gauss[j] : 0u;
   }
 #pragma unroll
   for (int i = 0; i < K2_ITEMS; ++i) {
     rc[i] = live[i] ? __ldg(&p.rect[g[i]]) : make_uint2(0u, 0u);
-    const uint32_t w = (rc[i].x >> 16) - (rc[i].x & 0xffffu) + 1, h = (rc[i].y >> 16) - (rc[i].y & 0xffffu) + 1;
-    cnt[i] = live[i] ? w * h : 0u;
-    sm.prefix[i * K2_THREADS + tid] = cnt[i];
+    const uint32_t c0 = rc[i].x & 0xffffu, c1 = rc[i].x >> 16, r0 = rc[i].y & 0xffffu, r1 = rc[i].y >> 16;
+    uint32_t c = 0;
+    if (live[i] && r1 >= r0) {
+      if (!CHECK_DONE) c = (c1 - c0 + 1) * (r1 - r0 + 1);
+      else   // tiles of the rectangle that are still being blended
+        for (uint32_t ty = r0; ty <= r1; ++ty)
+          for (uint32_t tx = c0; tx <= c1; ++tx)
+            c += tile_live<CHECK_DONE>(tile_done, ty * (uint32_t)tiles_across + tx) ? 1u : 0u;
+    }
+    cnt[i] = c;
+    sm.prefix[i * K2_THREADS + tid] = c;
   }
   __syncthreads();
   // exclusive scan of the chunk in position order: thread tid owns entries [tid*ITEMS, (tid+1)*ITEMS)
@@ -162,18 +201,21 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
   // The CTA's duplicates are the contiguous run [base, base + total).  Neighbouring threads own
   // neighbouring entries, so a warp's stores fall into one short contiguous span.  Small
   // rectangles (the common case: 3.4 tiles on average) are written by their own thread; the rare
-  // large ones are queued and written by the whole CTA so they do not serialise one thread.
+  // large ones are queued and written warp by warp so they do not serialise one thread.
 #pragma unroll
   for (int i = 0; i < K2_ITEMS; ++i) {
     if (cnt[i] == 0) continue;
     const uint32_t e = i * K2_THREADS + tid;
-    if (cnt[i] <= K2_SMALL) {   // row-major walk of the rectangle without divisions
-      const uint32_t c0 = rc[i].x & 0xffffu, c1 = rc[i].x >> 16;
+    const uint32_t c0 = rc[i].x & 0xffffu, c1 = rc[i].x >> 16;
+    const uint32_t area = (c1 - c0 + 1) * ((rc[i].y >> 16) - (rc[i].y & 0xffffu) + 1);
+    if (area <= K2_SMALL) {   // row-major walk of the rectangle without divisions
       uint32_t at = base + sm.prefix[e], tx = c0, row = (rc[i].y & 0xffffu) * (uint32_t)tiles_across;
-      for (uint32_t q = 0; q < cnt[i]; ++q) {
-        keys[at] = row + tx;
-        vals[at] = g[i];
-        ++at;
+      for (uint32_t q = 0; q < area; ++q) {
+        if (tile_live<CHECK_DONE>(tile_done, row + tx)) {
+          keys[at] = row + tx;
+          vals[at] = g[i];
+          ++at;
+        }
         if (tx == c1) { tx = c0; row += (uint32_t)tiles_across; } else { ++tx; }
       }
     } else {
@@ -183,26 +225,96 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
   }
   __syncthreads();
   const uint32_t n_big = sm.n_big;
-  for (uint32_t s = 0; s < n_big; ++s) {
-    const uint2 r = sm.big_rect[s];
-    const uint32_t w = (r.x >> 16) - (r.x & 0xffffu) + 1, h = (r.y >> 16) - (r.y & 0xffffu) + 1;
-    emit_rect(keys, vals, base + sm.prefix[sm.big[s]], r, sm.big_gauss[s], tiles_across, tid, K2_THREADS, w * h);
-  }
+  for (uint32_t s = tid >> 5; s < n_big; s += K2_THREADS / 32)
+    emit_rect_warp<CHECK_DONE>(keys, vals, base + sm.prefix[sm.big[s]], sm.big_rect[s], sm.big_gauss[s], tiles_across,
+                               tile_done, tid & 31);
 }
 
-void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t n,
-                      int tiles_across, uint32_t *keys, uint32_t *vals, uint32_t capacity,
-                      unsigned long long *lookback, uint32_t *ticket, uint32_t *total, uint32_t *overflow,
-                      cudaStream_t st) {
-  if (!n) return;
+void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t begin,
+                      uint32_t end, int tiles_across, const uint8_t *tile_done, uint32_t *keys, uint32_t *vals,
+                      uint32_t capacity, unsigned long long *lookback, uint32_t *ticket, uint32_t *total,
+                      uint32_t *overflow, cudaStream_t st) {
+  if (end <= begin) return;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(duplicate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem));
+    cudaFuncSetAttribute(duplicate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem));
+    cudaFuncSetAttribute(duplicate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem));
     attr_set = true;
   }
   ++g_launches;
-  duplicate_kernel<<<ceil_div(n, K2_CHUNK), K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_keys, sorted_gauss, n, tiles_across, keys,
-                                                                  vals, capacity, lookback, ticket, total, overflow);
+  const int grid = ceil_div(end - begin, K2_CHUNK);
+  if (tile_done)
+    duplicate_kernel<true><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_keys, sorted_gauss, begin, end, tiles_across,
+                                                                     tile_done, keys, vals, capacity, lookback, ticket,
+                                                                     total, overflow);
+  else
+    duplicate_kernel<false><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_keys, sorted_gauss, begin, end, tiles_across,
+                                                                      nullptr, keys, vals, capacity, lookback, ticket,
+                                                                      total, overflow);
+}
+
+// ---- a11: per-tile counts of the reference (codelets.cpp:501-504; getIPUHistogram) ---------------
+// counts[tile] = number of drawn Gaussians whose rectangle covers the tile = the length of the
+// reference's render list, whether or not the depth slices ever emit that far.  Each rectangle
+// adds +1/-1 at its four corners of a (rows+1) x (cols+1) difference grid (shared-memory copy per
+// CTA, flushed with one atomic per touched cell); a 2-D prefix sum turns the grid into counts.
+__global__ void __launch_bounds__(256)
+tile_count_kernel(Projected p, uint32_t n, int tiles_across, int tiles_down, int *__restrict__ diff) {
+  extern __shared__ int sdiff[];
+  const int gw = tiles_across + 1, cells = gw * (tiles_down + 1);
+  for (int k = threadIdx.x; k < cells; k += blockDim.x) sdiff[k] = 0;
+  __syncthreads();
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint2 rc = p.rect[i];
+    const int c0 = rc.x & 0xffffu, c1 = rc.x >> 16, r0 = rc.y & 0xffffu, r1 = rc.y >> 16;
+    if (c1 < c0 || r1 < r0) continue;   // not drawn (RECT_EMPTY), or outside this context's band
+    atomicAdd(&sdiff[r0 * gw + c0], 1);
+    atomicAdd(&sdiff[r0 * gw + c1 + 1], -1);
+    atomicAdd(&sdiff[(r1 + 1) * gw + c0], -1);
+    atomicAdd(&sdiff[(r1 + 1) * gw + c1 + 1], 1);
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < cells; k += blockDim.x)
+    if (sdiff[k]) atomicAdd(&diff[k], sdiff[k]);
+}
+
+// single CTA: 2-D inclusive prefix of the difference grid -> counts; clears the grid for the next frame
+__global__ void __launch_bounds__(1024)
+tile_count_finish_kernel(int *__restrict__ diff, int tiles_across, int tiles_down, uint32_t *__restrict__ counts) {
+  extern __shared__ int sgrid[];
+  const int gw = tiles_across + 1, gh = tiles_down + 1, cells = gw * gh;
+  for (int k = threadIdx.x; k < cells; k += blockDim.x) { sgrid[k] = diff[k]; diff[k] = 0; }
+  __syncthreads();
+  for (int r = threadIdx.x; r < gh; r += blockDim.x) {
+    int run = 0;
+    for (int c = 0; c < gw; ++c) { run += sgrid[r * gw + c]; sgrid[r * gw + c] = run; }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < gw; c += blockDim.x) {
+    int run = 0;
+    for (int r = 0; r < gh; ++r) { run += sgrid[r * gw + c]; sgrid[r * gw + c] = run; }
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < tiles_across * tiles_down; k += blockDim.x)
+    counts[k] = (uint32_t)sgrid[(k / tiles_across) * gw + k % tiles_across];
+}
+
+size_t tile_count_smem(int tiles_across, int tiles_down) {
+  return sizeof(int) * (size_t)(tiles_across + 1) * (tiles_down + 1);
+}
+
+void launch_tile_counts(const Projected &p, uint32_t n, int tiles_across, int tiles_down, int *diff, uint32_t *counts,
+                        cudaStream_t st) {
+  const size_t smem = tile_count_smem(tiles_across, tiles_down);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(tile_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_COUNT_MAX_SMEM);
+    cudaFuncSetAttribute(tile_count_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_COUNT_MAX_SMEM);
+    attr_set = true;
+  }
+  g_launches += n ? 2 : 1;
+  if (n) tile_count_kernel<<<148 * 2, 256, smem, st>>>(p, n, tiles_across, tiles_down, diff);
+  tile_count_finish_kernel<<<1, 1024, smem, st>>>(diff, tiles_across, tiles_down, counts);
 }
 
 }  // namespace gsplat

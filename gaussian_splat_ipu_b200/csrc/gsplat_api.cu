@@ -7,6 +7,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -16,7 +17,10 @@ using namespace gsplat;
 namespace {
 thread_local std::string g_create_error;
 
-enum Ev { EV_START = 0, EV_K1, EV_SORTA, EV_K2, EV_SORTB, EV_K4, EV_K5, EV_COUNT };
+// stage events of a frame: start, K1, sort A, then {K2, sort B, K4, K5} per depth slice
+constexpr int MAX_SLICES = GSPLAT_MAX_DEPTH_SLICES;
+enum Ev { EV_START = 0, EV_K1, EV_SORTA, EV_SLICE0, EV_COUNT = EV_SLICE0 + 4 * MAX_SLICES };
+enum SliceEv { SEV_K2 = 0, SEV_SORTB, SEV_K4, SEV_K5 };
 }  // namespace
 
 // One in-flight frame: its stage events and the pinned words its scalars are copied to.  Frames
@@ -26,7 +30,8 @@ constexpr int NUM_SLOTS = 4;
 struct FrameSlot {
   cudaEvent_t ev[EV_COUNT]{};
   cudaEvent_t done = nullptr;
-  uint32_t *h = nullptr;   // pinned: [0] D  [1] V  [2] overflow
+  uint32_t *h = nullptr;   // pinned copy of the frame's device scalars (enum Scalar)
+  int num_slices = 1;
   bool pending = false, timed = false, overflowed = false;
   uint64_t frame_no = 0;
 };
@@ -43,7 +48,11 @@ struct StreamSlot {
 };
 
 // device scalars
-enum Scalar { SC_D = 0, SC_V, SC_OVERFLOW, SC_TICKET, SC_N, SC_SORT_N, SC_COUNT = 16 };
+// device scalars; words [0, SC_FRAME_WORDS) are zeroed at the start of every frame and copied to
+// the frame slot's pinned words at its end
+enum Scalar { SC_V = 0, SC_OVERFLOW = 1, SC_TICKET0 = 8 /* K2 chain ticket per slice */,
+              SC_DS0 = 16 /* duplicates emitted per slice */, SC_FRAME_WORDS = 24, SC_N = 24, SC_SORT_N = 25,
+              SC_COUNT = 32 };
 
 struct gsplat_ctx {
   gsplat_config cfg{};
@@ -64,7 +73,19 @@ struct gsplat_ctx {
   unsigned long long *lookback = nullptr;
   uint32_t n_blocks = 0;
   uint2 *ranges = nullptr;
-  uint32_t *counts = nullptr;
+  uint32_t *counts = nullptr;      // a11: reference list length of every tile (tile_count_kernel)
+  int *count_diff = nullptr;       // difference grid of tile_count_kernel (kept zero between frames)
+  // depth slices (duplicate.cu): positions [slice_begin[s], slice_begin[s+1]) of the depth order
+  int num_slices = 1;
+  uint32_t slice_begin[MAX_SLICES + 1] = {0};
+  uint8_t *tile_state = nullptr;   // one block, zeroed per frame: TileState arrays
+  TileState ts{};                  // per tile / per part: every pixel has stopped
+  int blend_split = 1;             // K5 CTAs per semantic tile
+  float *tstate = nullptr;         // per pixel: transmittance carried between slices (-1 = stopped)
+  unsigned long long *pair_counters = nullptr;   // non-null while a counting re-run is enqueued
+  // parity tap: per-slice sorted lists of the last frame (filled only with cfg.debug_records)
+  std::vector<std::vector<uint2>> log_ranges;
+  std::vector<std::vector<uint32_t>> log_vals;
   float4 *fb = nullptr;
   uint8_t *bgr = nullptr;
   // state
@@ -128,6 +149,43 @@ int alloc_sort(gsplat_ctx *ctx, SortBuffers &s, size_t capacity) {
 
 int ceil_log2(uint32_t v) { int b = 0; while ((1u << b) < v) ++b; return b; }
 
+// Depth slices: cumulative fractions of the depth order at which the frame is cut.  The first
+// slice is small (dense tiles saturate within their first few thousand Gaussians: 1/16 of the
+// depth order with the default two slices), further cuts are spaced geometrically up to 1;
+// boundaries fall on K2 chunks.  depth_slices == 1: one slice (every tile's list
+// complete, the reference's lists).  GSPLAT_SLICE_FRACTIONS="f0,f1,...,1" overrides (experiments).
+void plan_slices(gsplat_ctx *ctx) {
+  const uint32_t n = ctx->scene.n;
+  int want = ctx->cfg.depth_slices ? ctx->cfg.depth_slices : GSPLAT_DEFAULT_DEPTH_SLICES;
+  double frac[MAX_SLICES];
+  for (int s = 0; s < want; ++s) frac[s] = std::pow(0.0625, (double)(want - 1 - s) / (want > 2 ? 0.5 * (want - 1) : 1.0));
+  if (const char *e = std::getenv("GSPLAT_SLICE_FRACTIONS")) {
+    if (!ctx->cfg.depth_slices) {
+      int k = 0;
+      const char *q = e;
+      while (*q && k < MAX_SLICES) {
+        char *end = nullptr;
+        const double v = std::strtod(q, &end);
+        if (end == q) break;
+        frac[k++] = v;
+        q = *end == ',' ? end + 1 : end;
+      }
+      if (k) { want = k; frac[k - 1] = 1.0; }
+    }
+  }
+  int ns = 0;
+  uint32_t last = 0;
+  ctx->slice_begin[0] = 0;
+  for (int s = 0; s + 1 < want; ++s) {
+    uint64_t b = (uint64_t)((double)n * frac[s]);
+    b = (b + K2_CHUNK - 1) / K2_CHUNK * K2_CHUNK;
+    if (b >= n) break;
+    if (b > last) { ctx->slice_begin[++ns] = (uint32_t)b; last = (uint32_t)b; }
+  }
+  ctx->slice_begin[++ns] = n;
+  ctx->num_slices = ns;
+}
+
 // glm type_mat4x4.inl:630-648, left-to-right sums; column-major 16-float arrays
 void mat4_mul(const float *a, const float *b, float *r) {
   for (int c = 0; c < 4; ++c)
@@ -163,6 +221,7 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->d_scalars); dfree(ctx->lookback);
   free_sort(ctx->sort_a); free_sort(ctx->sort_b);
   dfree(ctx->ranges); dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
+  dfree(ctx->count_diff); dfree(ctx->tile_state); dfree(ctx->tstate);
   if (ctx->copy_st) cudaStreamSynchronize(ctx->copy_st);
   for (auto &ss : ctx->sslots) {
     dfree(ss.d_bgr); dfree(ss.d_counts);
@@ -196,6 +255,10 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: K5 supports tile_w == 32 and tile_h in {4,8,...,32}");
   if (cfg->width / cfg->tile_w > 65535 || cfg->height / cfg->tile_h > 65535)
     return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: tile grid exceeds 16-bit tile coordinates");
+  if (tile_count_smem(cfg->width / cfg->tile_w, cfg->height / cfg->tile_h) > TILE_COUNT_MAX_SMEM)
+    return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: tile grid too large for the per-tile count kernel");
+  if (cfg->depth_slices < 0 || cfg->depth_slices > GSPLAT_MAX_DEPTH_SLICES)
+    return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: depth_slices must be 0 (default) .. GSPLAT_MAX_DEPTH_SLICES");
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0)
@@ -224,12 +287,12 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   } while (0)
   CUC(cudaSetDevice(cfg->device));
   CUC(cudaStreamCreateWithFlags(&ctx->st, cudaStreamNonBlocking));
-  CUC(cudaHostAlloc(&ctx->h_scalars, NUM_SLOTS * 4 * sizeof(uint32_t), cudaHostAllocDefault));
+  CUC(cudaHostAlloc(&ctx->h_scalars, NUM_SLOTS * SC_FRAME_WORDS * sizeof(uint32_t), cudaHostAllocDefault));
   for (int k = 0; k < NUM_SLOTS; ++k) {
     FrameSlot &sl = ctx->slots[k];
     for (auto &ev : sl.ev) CUC(cudaEventCreate(&ev));
     CUC(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
-    sl.h = ctx->h_scalars + 4 * k;
+    sl.h = ctx->h_scalars + SC_FRAME_WORDS * k;
   }
   CUC(cudaEventCreate(&ctx->t0));
   CUC(cudaEventCreate(&ctx->t1));
@@ -248,6 +311,24 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   CUC(cudaMemset(ctx->bgr, 0, px * 3));
   CUC(cudaMemset(ctx->counts, 0, sizeof(uint32_t) * ctx->num_tiles));
   CUC(cudaMemset(ctx->ranges, 0, sizeof(uint2) * ctx->num_tiles));
+  {
+    const size_t grid = (size_t)(ctx->tiles_across + 1) * (ctx->tiles_down + 1);
+    CUC(cudaMalloc(&ctx->count_diff, sizeof(int) * grid));
+    CUC(cudaMemset(ctx->count_diff, 0, sizeof(int) * grid));
+    const size_t tsb = tile_state_bytes(ctx->num_tiles);
+    CUC(cudaMalloc(&ctx->tile_state, tsb));
+    CUC(cudaMemset(ctx->tile_state, 0, tsb));
+    const size_t T4 = ((size_t)ctx->num_tiles + 3) / 4 * 4;
+    ctx->ts.parts_done = reinterpret_cast<uint32_t *>(ctx->tile_state);
+    ctx->ts.tile_done = ctx->tile_state + 4 * T4;
+    ctx->ts.part_done = ctx->ts.tile_done + T4;
+    // K5 CTAs per tile: two half-tiles when the tile height allows (GSPLAT_K5_SPLIT overrides)
+    int split = cfg->tile_h % 2 == 0 && cfg->tile_h / 2 >= 4 ? 2 : 1;
+    if (const char *e = std::getenv("GSPLAT_K5_SPLIT")) split = std::atoi(e);
+    if (split < 1 || split > BLEND_MAX_SPLIT || cfg->tile_h % split) split = 1;
+    ctx->blend_split = split;
+    CUC(cudaMalloc(&ctx->tstate, sizeof(float) * px));
+  }
 #undef CUC
   *out = ctx;
   return GSPLAT_OK;
@@ -273,7 +354,8 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   CU(cudaMemsetAsync(ctx->proj.rec, 0, na * 3 * sizeof(float4), ctx->st));
   CU(cudaMalloc(&ctx->proj.rect, na * sizeof(uint2)));
   ctx->n_blocks = (uint32_t)((n + K2_CHUNK - 1) / K2_CHUNK);
-  CU(cudaMalloc(&ctx->lookback, (ctx->n_blocks + 1) * sizeof(unsigned long long)));
+  CU(cudaMalloc(&ctx->lookback, (size_t)MAX_SLICES * (ctx->n_blocks + 1) * sizeof(unsigned long long)));
+  plan_slices(ctx);
   if (ctx->cfg.debug_records) {
     CU(cudaMalloc(&ctx->dbg_rec8, na * 8 * sizeof(float)));
     CU(cudaMalloc(&ctx->dbg_rect4, na * 4 * sizeof(int32_t)));

@@ -45,6 +45,7 @@ struct Projected {
                          // order, and a random 8 B read costs one 32 B sector instead of a 48 B record
 };
 constexpr uint32_t DEPTH_KEY_CULLED = 0xffffffffu;
+constexpr uint32_t RECT_EMPTY = 1u;   // {lo = 1, hi = 0}: the rectangle of a Gaussian that is not drawn
 
 constexpr int K1_THREADS = 256;
 
@@ -78,34 +79,48 @@ void sort_plan(int nbits, int &passes, int &bits_per_pass);
 int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,
                       bool identity_vals, cudaStream_t st);
 
-// K2: walks the Gaussians in DEPTH order (sorted_gauss = values of sort A) and emits one
-// (tile id, Gaussian index) pair per tile of each drawn Gaussian's rectangle.  Offsets come from a
-// single-pass chained scan (decoupled look-back over `lookback`, which must be zeroed — together
-// with *ticket — before each launch), so the output is in (depth, gid, tile) order and
-// bit-reproducible.  Writes D to *total; sets *overflow (and writes nothing past the buffer) if
-// D > capacity.
+// K2: walks positions [begin, end) of the DEPTH order (sorted_gauss = values of sort A) and emits
+// one (tile id, Gaussian index) pair per tile of each drawn Gaussian's rectangle — skipping tiles
+// whose tile_done flag is set when tile_done != nullptr (depth slices, duplicate.cu).  Offsets come
+// from a single-pass chained scan (decoupled look-back over `lookback`, which must be zeroed —
+// together with *ticket — before each launch), so the output is in (depth, gid, tile) order and
+// bit-reproducible.  Writes the number of pairs to *total; sets *overflow (and writes nothing past
+// the buffer) if it exceeds capacity.
 constexpr int K2_THREADS = 256;
 constexpr int K2_ITEMS = 4;
 constexpr int K2_LOG_CHUNK = 10;
 constexpr int K2_CHUNK = K2_THREADS * K2_ITEMS;   // Gaussians per CTA == per chain link
 static_assert((1 << K2_LOG_CHUNK) == K2_CHUNK, "binary search depth");
-void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t n,
-                      int tiles_across, uint32_t *keys, uint32_t *vals, uint32_t capacity,
-                      unsigned long long *lookback, uint32_t *ticket, uint32_t *total, uint32_t *overflow,
-                      cudaStream_t st);
+void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t begin,
+                      uint32_t end, int tiles_across, const uint8_t *tile_done, uint32_t *keys, uint32_t *vals,
+                      uint32_t capacity, unsigned long long *lookback, uint32_t *ticket, uint32_t *total,
+                      uint32_t *overflow, cudaStream_t st);
+// a11: counts[tile] = drawn Gaussians whose rectangle covers the tile (the reference's list length).
+// `diff` is a (tiles_down+1) x (tiles_across+1) int grid that must be zero on entry and is left zero.
+constexpr size_t TILE_COUNT_MAX_SMEM = 200 * 1024;
+size_t tile_count_smem(int tiles_across, int tiles_down);
+void launch_tile_counts(const Projected &p, uint32_t n, int tiles_across, int tiles_down, int *diff, uint32_t *counts,
+                        cudaStream_t st);
 
 // K4: per-tile [start,end) over the sorted tile keys.
 void launch_tile_ranges(const uint32_t *keys, const uint32_t *d_n, uint32_t n_upper, uint32_t cap,
                         uint2 *ranges, uint32_t num_tiles, cudaStream_t st);
 
-// K5: front-to-back blend of every tile of the band, writes the tile-major f32 framebuffer and
-// the per-tile counts.
-void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges,
-                  const FrameParams &fp, float4 *fb_tiled, uint32_t *counts, cudaStream_t st);
-// counting variant (roofline accounting): pair_counters[0] += visited pairs, [1] += blended pairs
-void launch_blend_count(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges,
-                        const FrameParams &fp, float4 *fb_tiled, uint32_t *counts,
-                        unsigned long long *pair_counters, cudaStream_t st);
+// K5: front-to-back blend of every tile of the band over one depth slice's lists; `first`/`last`
+// say whether pixel state is initialised / saved (tstate: T per pixel, -1 = stopped; tile_done: all
+// pixels of the tile stopped).  pair_counters != nullptr selects the counting variant (roofline
+// accounting): [0] += visited pairs, [1] += blended pairs, then per tile {cycles, visited pairs}.
+// `split`: CTAs per semantic tile (each blends tile_h / split rows; must divide tile_h).
+struct TileState {
+  uint8_t *tile_done;    // [tiles] every pixel of the tile has stopped (read by K2 of later slices)
+  uint8_t *part_done;    // [tiles * BLEND_MAX_SPLIT] every pixel of the part has stopped
+  uint32_t *parts_done;  // [tiles] parts of the tile that have stopped
+};
+constexpr int BLEND_MAX_SPLIT = 8;
+inline size_t tile_state_bytes(int tiles) { return (size_t)tiles * (1 + BLEND_MAX_SPLIT + 4) + 16; }
+void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
+                  float4 *fb_tiled, float *tstate, const TileState &ts, int split, bool first, bool last,
+                  unsigned long long *pair_counters, cudaStream_t st);
 
 // a10: tiled f32 RGBA -> de-tiled BGR8 rows.
 void launch_bgr8(const float4 *fb_tiled, uint8_t *bgr, int W, int H, int tile_w, int tile_h,

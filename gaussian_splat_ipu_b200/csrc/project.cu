@@ -182,6 +182,7 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
     // depth key: drawn Gaussians have clip z < 0 (codelets.cpp:493); ascending z (:314) ==
     // descending magnitude == ascending ~bits(z); everything else sorts last
     out.depth_key[i] = touched ? ~__float_as_uint(cz) : DEPTH_KEY_CULLED;
+    if (!touched) out.rect[i] = make_uint2(RECT_EMPTY, RECT_EMPTY);   // c0 > c1: covers no tile
     if (dbg_rec8) {
       float4 *d = reinterpret_cast<float4 *>(dbg_rec8 + (size_t)i * 8);
       d[0] = make_float4(px, py, cz, cova);
@@ -218,6 +219,7 @@ inject_kernel(const float *__restrict__ depth, const int32_t *__restrict__ rect4
       }
     }
     out.depth_key[i] = touched ? ~__float_as_uint(z) : DEPTH_KEY_CULLED;
+    if (!touched) out.rect[i] = make_uint2(RECT_EMPTY, RECT_EMPTY);
   }
   const uint32_t nd = block_sum<K1_THREADS>(touched ? 1u : 0u, red);
   if (threadIdx.x == 0 && nd) atomicAdd(drawn_counter, nd);

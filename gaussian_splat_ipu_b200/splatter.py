@@ -33,13 +33,14 @@ class Config(C.Structure):
     _fields_ = [("device", C.c_int), ("width", C.c_int), ("height", C.c_int), ("tile_w", C.c_int),
                 ("tile_h", C.c_int), ("guard_factor", C.c_float), ("band_row_begin", C.c_int),
                 ("band_row_end", C.c_int), ("collect_timings", C.c_int), ("debug_records", C.c_int),
-                ("dup_capacity", C.c_size_t)]
+                ("dup_capacity", C.c_size_t), ("depth_slices", C.c_int)]
 
 
 class FrameStats(C.Structure):
     _fields_ = [("num_gaussians", C.c_uint64), ("num_drawn", C.c_uint64), ("num_duplicates", C.c_uint64),
                 ("dup_capacity", C.c_uint64), ("max_tile_count", C.c_uint32), ("num_tiles", C.c_uint32),
-                ("regrown", C.c_uint32), ("key_bits", C.c_uint32)]
+                ("regrown", C.c_uint32), ("key_bits", C.c_uint32), ("num_reference_duplicates", C.c_uint64),
+                ("depth_slices", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 # every symbol include/gsplat_b200.h declares: name -> (restype, argtypes)
@@ -158,7 +159,7 @@ class B200Splatter:
     ``getIPUHistogram``."""
 
     def __init__(self, gaussians16: np.ndarray, width=1280, height=720, tile_w=32, tile_h=20, device=0,
-                 band=None, collect_timings=False, debug_records=False, dup_capacity=0):
+                 band=None, collect_timings=False, debug_records=False, dup_capacity=0, depth_slices=0):
         self.lib = load_library()
         cfg = Config()
         self.lib.gsplat_config_default(C.byref(cfg))
@@ -166,6 +167,7 @@ class B200Splatter:
         if band is not None:
             cfg.band_row_begin, cfg.band_row_end = band
         cfg.collect_timings, cfg.debug_records, cfg.dup_capacity = int(collect_timings), int(debug_records), dup_capacity
+        cfg.depth_slices = int(depth_slices)   # 0 = library default; 1 = complete (reference) lists
         self.cfg = cfg
         self.h = _vp()
         rc = self.lib.gsplat_create(C.byref(cfg), C.byref(self.h))

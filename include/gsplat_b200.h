@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define GSPLAT_ABI_VERSION 1
+#define GSPLAT_ABI_VERSION 2
 
 typedef enum gsplat_status {
   GSPLAT_OK = 0,
@@ -56,7 +56,15 @@ typedef struct gsplat_config {
   int debug_records;     /* K1 also writes the projected records for gsplat_read_projected    */
   size_t dup_capacity;   /* initial capacity of the (tile,Gaussian) duplicate buffers;        */
                          /* 0 = choose from the scene size; grows on demand                   */
+  int depth_slices;      /* the frame is binned and blended in this many slices of the depth  */
+                         /* order, nearest first; tiles whose pixels have all stopped          */
+                         /* (test_T < 1e-4, codelets.cpp:405-408) drop out of the later slices. */
+                         /* 1 = one slice: every tile's list is the reference's complete list.  */
+                         /* 0 = default (GSPLAT_DEFAULT_DEPTH_SLICES).  Framebuffer and counts   */
+                         /* do not depend on it; lists are exact prefixes of the reference's.   */
 } gsplat_config;
+#define GSPLAT_MAX_DEPTH_SLICES 8
+#define GSPLAT_DEFAULT_DEPTH_SLICES 2
 
 /* Fills *cfg with the reference defaults (1280x720, 32x20, guard 15, device 0). */
 int gsplat_config_default(gsplat_config *cfg);
@@ -132,12 +140,16 @@ int gsplat_acquire_frame(gsplat_ctx *ctx, uint64_t ticket, const uint8_t **bgr8,
 typedef struct gsplat_frame_stats {
   uint64_t num_gaussians; /* N                                             */
   uint64_t num_drawn;     /* V: Gaussians passing the render predicate      */
-  uint64_t num_duplicates;/* D: sum of per-tile list lengths                */
+  uint64_t num_duplicates;/* D: (tile, Gaussian) pairs binned = sum of the list lengths  */
+                          /* actually built (depth slices stop at saturated tiles)      */
   uint64_t dup_capacity;  /* current capacity of the duplicate buffers      */
   uint32_t max_tile_count;
   uint32_t num_tiles;     /* tiles_across * tiles_down                      */
   uint32_t regrown;       /* 1 if this frame had to be re-run after growing */
   uint32_t key_bits;      /* sorted key width: 32 depth bits + tile-id bits */
+  uint64_t num_reference_duplicates; /* sum of the per-tile counts = D of the reference's lists */
+  uint32_t depth_slices;  /* slices the frame was cut into                   */
+  uint32_t reserved;
 } gsplat_frame_stats;
 int gsplat_get_frame_stats(gsplat_ctx *ctx, gsplat_frame_stats *out);
 
@@ -157,7 +169,9 @@ int gsplat_get_timings_accum(gsplat_ctx *ctx, double *ms_sum, uint64_t *frames, 
  * cov_b, cov_c, radius, drawn}; rect4 = n x {c0, c1, r0, r1} tile rectangle (valid iff drawn). */
 int gsplat_read_projected(gsplat_ctx *ctx, float *rec8, int32_t *rect4);
 /* Per-tile render lists of the last frame: offsets[num_tiles+1], lists[offsets[num_tiles]]
- * (Gaussian index = gid-1, in blend order).  lists may be NULL to query sizes only. */
+ * (Gaussian index = gid-1, in blend order).  lists may be NULL to query sizes only.  With more than
+ * one depth slice the lists of all slices are only kept when debug_records is set; a tile's list is
+ * then the reference's list cut after the slice in which the tile saturated. */
 int gsplat_read_tile_lists(gsplat_ctx *ctx, int64_t *offsets, int32_t *lists, size_t lists_capacity);
 /* Runs K2-K4 (and K5 when `blend` != 0) from caller-supplied projected inputs instead of K1's:
  * depth[n] = clip z, rect4 as above, drawn[n] (0/1).  K5 then uses the records of the last
