@@ -66,8 +66,8 @@ __device__ __forceinline__ void st_relaxed(unsigned long long *p, unsigned long 
 // Depth slices.  K5 stops a pixel at the first Gaussian that would push its transmittance under
 // 1e-4 (codelets.cpp:405-408); once every pixel of a tile has stopped, nothing further down the
 // tile's list can change the image.  The frame is therefore binned and blended in a few slices of
-// the depth order, nearest first: one launch covers positions [begin, end) of the depth order and,
-// when CHECK_DONE, emits nothing for tiles whose `tile_done` flag K5 raised in an earlier slice.
+// increasing depth (select.cu): one launch walks the depth-sorted Gaussians of one slice and, when
+// CHECK_DONE, emits nothing for tiles whose `tile_done` flag K5 raised in an earlier slice.
 // Every tile's list is then an exact PREFIX of the reference's list — complete unless the tile
 // saturated — and the framebuffer is bit-identical to the one-slice run.  The per-tile COUNTS of
 // the reference (codelets.cpp:501-504) still count every Gaussian: tile_count_kernel below.
@@ -116,14 +116,19 @@ __device__ __forceinline__ void emit_rect_warp(uint32_t *__restrict__ keys, uint
 
 template <bool CHECK_DONE>
 __global__ void __launch_bounds__(K2_THREADS)
-duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const uint32_t *__restrict__ sorted_gauss,
-                 uint32_t begin, uint32_t end, int tiles_across, const uint8_t *__restrict__ tile_done,
-                 uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t capacity,
+duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_gauss, const uint32_t *__restrict__ d_count,
+                 uint32_t count_cap, int tiles_across, const uint8_t *__restrict__ tile_done,
+                 const uint32_t *__restrict__ live_sat, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t capacity,
                  unsigned long long *__restrict__ lookback, uint32_t *__restrict__ ticket,
                  uint32_t *__restrict__ total_out, uint32_t *__restrict__ overflow) {
   extern __shared__ __align__(16) unsigned char k2_smem_raw[];
   K2Smem &sm = *reinterpret_cast<K2Smem *>(k2_smem_raw);
   const uint32_t tid = threadIdx.x;
+  // the slice's Gaussian count is only known on the device: the grid covers the capacity and the
+  // CTAs beyond the last chunk leave at once (before taking a chain ticket)
+  const uint32_t end = min(*d_count, count_cap);
+  const uint32_t nblk = (end + K2_CHUNK - 1) / K2_CHUNK;
+  if (blockIdx.x >= nblk) return;
   if (tid == 0) { sm.chain = atomicAdd(ticket, 1u); sm.n_big = 0; }
   __syncthreads();
   const uint32_t b = sm.chain;
@@ -133,8 +138,8 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
   bool live[K2_ITEMS];
 #pragma unroll
   for (int i = 0; i < K2_ITEMS; ++i) {
-    const uint32_t j = begin + b * K2_CHUNK + i * K2_THREADS + tid;   // position in depth order
-    live[i] = j < end && sorted_keys[j] != DEPTH_KEY_CULLED;
+    const uint32_t j = b * K2_CHUNK + i * K2_THREADS + tid;   // position in the slice's depth order
+    live[i] = j < end;
     g[i] = live[i] ? sorted_gauss[j] : 0u;
   }
 #pragma unroll
@@ -144,10 +149,7 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
     uint32_t c = 0;
     if (live[i] && r1 >= r0) {
       if (!CHECK_DONE) c = (c1 - c0 + 1) * (r1 - r0 + 1);
-      else   // tiles of the rectangle that are still being blended
-        for (uint32_t ty = r0; ty <= r1; ++ty)
-          for (uint32_t tx = c0; tx <= c1; ++tx)
-            c += tile_live<CHECK_DONE>(tile_done, ty * (uint32_t)tiles_across + tx) ? 1u : 0u;
+      else c = live_tiles_in_rect(live_sat, tiles_across, c0, c1, r0, r1);   // tiles still being blended
     }
     cnt[i] = c;
     sm.prefix[i * K2_THREADS + tid] = c;
@@ -189,7 +191,7 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
     }
     if (tid == 0) {
       const unsigned long long incl = excl + total;
-      if (b == gridDim.x - 1) *total_out = incl > 0xffffffffull ? 0xffffffffu : (uint32_t)incl;
+      if (b == nblk - 1) *total_out = incl > 0xffffffffull ? 0xffffffffu : (uint32_t)incl;
       if (incl > capacity) atomicExch(overflow, 1u);   // never write past the buffer; the host re-runs
       sm.chain = incl > capacity ? 0xffffffffu : (uint32_t)excl;
     }
@@ -230,11 +232,11 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_keys, const ui
                                tile_done, tid & 31);
 }
 
-void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t begin,
-                      uint32_t end, int tiles_across, const uint8_t *tile_done, uint32_t *keys, uint32_t *vals,
+void launch_duplicate(const Projected &p, const uint32_t *sorted_gauss, const uint32_t *d_count, uint32_t count_cap,
+                      int tiles_across, const uint8_t *tile_done, const uint32_t *live_sat, uint32_t *keys, uint32_t *vals,
                       uint32_t capacity, unsigned long long *lookback, uint32_t *ticket, uint32_t *total,
                       uint32_t *overflow, cudaStream_t st) {
-  if (end <= begin) return;
+  if (!count_cap) return;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(duplicate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem));
@@ -242,15 +244,15 @@ void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uin
     attr_set = true;
   }
   ++g_launches;
-  const int grid = ceil_div(end - begin, K2_CHUNK);
+  const int grid = ceil_div(count_cap, K2_CHUNK);
   if (tile_done)
-    duplicate_kernel<true><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_keys, sorted_gauss, begin, end, tiles_across,
-                                                                     tile_done, keys, vals, capacity, lookback, ticket,
-                                                                     total, overflow);
+    duplicate_kernel<true><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_gauss, d_count, count_cap, tiles_across,
+                                                                     tile_done, live_sat, keys, vals, capacity, lookback,
+                                                                     ticket, total, overflow);
   else
-    duplicate_kernel<false><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_keys, sorted_gauss, begin, end, tiles_across,
-                                                                      nullptr, keys, vals, capacity, lookback, ticket,
-                                                                      total, overflow);
+    duplicate_kernel<false><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_gauss, d_count, count_cap, tiles_across,
+                                                                      nullptr, nullptr, keys, vals, capacity, lookback,
+                                                                      ticket, total, overflow);
 }
 
 // ---- a11: per-tile counts of the reference (codelets.cpp:501-504; getIPUHistogram) ---------------
@@ -258,20 +260,31 @@ void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uin
 // reference's render list, whether or not the depth slices ever emit that far.  Each rectangle
 // adds +1/-1 at its four corners of a (rows+1) x (cols+1) difference grid (shared-memory copy per
 // CTA, flushed with one atomic per touched cell); a 2-D prefix sum turns the grid into counts.
-__global__ void __launch_bounds__(256)
+constexpr int TC_THREADS = 1024;
+constexpr int TC_BATCH = 4;
+__global__ void __launch_bounds__(TC_THREADS)
 tile_count_kernel(Projected p, uint32_t n, int tiles_across, int tiles_down, int *__restrict__ diff) {
   extern __shared__ int sdiff[];
   const int gw = tiles_across + 1, cells = gw * (tiles_down + 1);
   for (int k = threadIdx.x; k < cells; k += blockDim.x) sdiff[k] = 0;
   __syncthreads();
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint2 rc = p.rect[i];
-    const int c0 = rc.x & 0xffffu, c1 = rc.x >> 16, r0 = rc.y & 0xffffu, r1 = rc.y >> 16;
-    if (c1 < c0 || r1 < r0) continue;   // not drawn (RECT_EMPTY), or outside this context's band
-    atomicAdd(&sdiff[r0 * gw + c0], 1);
-    atomicAdd(&sdiff[r0 * gw + c1 + 1], -1);
-    atomicAdd(&sdiff[(r1 + 1) * gw + c0], -1);
-    atomicAdd(&sdiff[(r1 + 1) * gw + c1 + 1], 1);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * TC_BATCH) {
+    uint2 rc[TC_BATCH];
+#pragma unroll
+    for (int k = 0; k < TC_BATCH; ++k) {   // TC_BATCH independent loads in flight per thread
+      const uint32_t i = i0 + k * stride;
+      rc[k] = i < n ? p.rect[i] : make_uint2(RECT_EMPTY, RECT_EMPTY);
+    }
+#pragma unroll
+    for (int k = 0; k < TC_BATCH; ++k) {
+      const int c0 = rc[k].x & 0xffffu, c1 = rc[k].x >> 16, r0 = rc[k].y & 0xffffu, r1 = rc[k].y >> 16;
+      if (c1 < c0 || r1 < r0) continue;   // not drawn (RECT_EMPTY), or outside this context's band
+      atomicAdd(&sdiff[r0 * gw + c0], 1);
+      atomicAdd(&sdiff[r0 * gw + c1 + 1], -1);
+      atomicAdd(&sdiff[(r1 + 1) * gw + c0], -1);
+      atomicAdd(&sdiff[(r1 + 1) * gw + c1 + 1], 1);
+    }
   }
   __syncthreads();
   for (int k = threadIdx.x; k < cells; k += blockDim.x)
@@ -299,6 +312,42 @@ tile_count_finish_kernel(int *__restrict__ diff, int tiles_across, int tiles_dow
     counts[k] = (uint32_t)sgrid[(k / tiles_across) * gw + k % tiles_across];
 }
 
+size_t tile_count_smem(int tiles_across, int tiles_down);
+// Summed-area table of the tiles that are still being blended: sat[r * (cols+1) + c] = live tiles
+// in rows < r and columns < c.  Later slices ask "how many live tiles does this rectangle cover"
+// with four reads (select.cu, K2) instead of walking the rectangle.  Single CTA.
+__global__ void __launch_bounds__(1024)
+live_sat_kernel(const uint8_t *__restrict__ tile_done, int tiles_across, int tiles_down, uint32_t *__restrict__ sat) {
+  extern __shared__ int sgrid[];
+  const int gw = tiles_across + 1, gh = tiles_down + 1, cells = gw * gh;
+  for (int k = threadIdx.x; k < cells; k += blockDim.x) {
+    const int r = k / gw, c = k % gw;
+    sgrid[k] = (r > 0 && c > 0 && tile_done[(r - 1) * tiles_across + (c - 1)] == 0) ? 1 : 0;
+  }
+  __syncthreads();
+  for (int r = threadIdx.x; r < gh; r += blockDim.x) {
+    int run = 0;
+    for (int c = 0; c < gw; ++c) { run += sgrid[r * gw + c]; sgrid[r * gw + c] = run; }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < gw; c += blockDim.x) {
+    int run = 0;
+    for (int r = 0; r < gh; ++r) { run += sgrid[r * gw + c]; sgrid[r * gw + c] = run; }
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < cells; k += blockDim.x) sat[k] = (uint32_t)sgrid[k];
+}
+
+void launch_live_sat(const uint8_t *tile_done, int tiles_across, int tiles_down, uint32_t *sat, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(live_sat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_COUNT_MAX_SMEM);
+    attr_set = true;
+  }
+  ++g_launches;
+  live_sat_kernel<<<1, 1024, tile_count_smem(tiles_across, tiles_down), st>>>(tile_done, tiles_across, tiles_down, sat);
+}
+
 size_t tile_count_smem(int tiles_across, int tiles_down) {
   return sizeof(int) * (size_t)(tiles_across + 1) * (tiles_down + 1);
 }
@@ -313,7 +362,7 @@ void launch_tile_counts(const Projected &p, uint32_t n, int tiles_across, int ti
     attr_set = true;
   }
   g_launches += n ? 2 : 1;
-  if (n) tile_count_kernel<<<148 * 2, 256, smem, st>>>(p, n, tiles_across, tiles_down, diff);
+  if (n) tile_count_kernel<<<148 * 2, TC_THREADS, smem, st>>>(p, n, tiles_across, tiles_down, diff);
   tile_count_finish_kernel<<<1, 1024, smem, st>>>(diff, tiles_across, tiles_down, counts);
 }
 

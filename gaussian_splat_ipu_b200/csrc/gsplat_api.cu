@@ -17,10 +17,10 @@ using namespace gsplat;
 namespace {
 thread_local std::string g_create_error;
 
-// stage events of a frame: start, K1, sort A, then {K2, sort B, K4, K5} per depth slice
+// stage events of a frame: start, K1, then {select + sort A, K2, sort B, K4, K5} per depth slice
 constexpr int MAX_SLICES = GSPLAT_MAX_DEPTH_SLICES;
-enum Ev { EV_START = 0, EV_K1, EV_SORTA, EV_SLICE0, EV_COUNT = EV_SLICE0 + 4 * MAX_SLICES };
-enum SliceEv { SEV_K2 = 0, SEV_SORTB, SEV_K4, SEV_K5 };
+enum Ev { EV_START = 0, EV_K1, EV_SLICE0, EV_COUNT = EV_SLICE0 + 5 * MAX_SLICES };
+enum SliceEv { SEV_SORTA = 0, SEV_K2, SEV_SORTB, SEV_K4, SEV_K5, SEV_COUNT };
 }  // namespace
 
 // One in-flight frame: its stage events and the pinned words its scalars are copied to.  Frames
@@ -51,8 +51,9 @@ struct StreamSlot {
 // device scalars; words [0, SC_FRAME_WORDS) are zeroed at the start of every frame and copied to
 // the frame slot's pinned words at its end
 enum Scalar { SC_V = 0, SC_OVERFLOW = 1, SC_TICKET0 = 8 /* K2 chain ticket per slice */,
-              SC_DS0 = 16 /* duplicates emitted per slice */, SC_FRAME_WORDS = 24, SC_N = 24, SC_SORT_N = 25,
-              SC_COUNT = 32 };
+              SC_DS0 = 16 /* duplicates emitted per slice */, SC_NS0 = 24 /* Gaussians selected per slice */,
+              SC_SELTICKET0 = 32 /* selection chain ticket per slice */, SC_TAU0 = 40 /* depth-key thresholds */,
+              SC_FRAME_WORDS = 48, SC_N = 48, SC_SORT_N = 49, SC_COUNT = 64 };
 
 struct gsplat_ctx {
   gsplat_config cfg{};
@@ -71,13 +72,15 @@ struct gsplat_ctx {
   SortBuffers sort_a{}, sort_b{};
   int sorted_a = 0, sorted = 0;    // which of sort_x.keys/vals holds the sorted result
   unsigned long long *lookback = nullptr;
-  uint32_t n_blocks = 0;
+  uint32_t n_blocks = 0, n_sel_blocks = 0;
   uint2 *ranges = nullptr;
   uint32_t *counts = nullptr;      // a11: reference list length of every tile (tile_count_kernel)
   int *count_diff = nullptr;       // difference grid of tile_count_kernel (kept zero between frames)
-  // depth slices (duplicate.cu): positions [slice_begin[s], slice_begin[s+1]) of the depth order
+  uint32_t *live_sat = nullptr;    // summed-area table of the tiles still being blended (depth slices)
+  // depth slices (select.cu): slice s = depth keys in [tau[s-1], tau[s]), tau = sampled quantiles
   int num_slices = 1;
-  uint32_t slice_begin[MAX_SLICES + 1] = {0};
+  SliceFractions slice_fr{};       // cumulative fractions of the thresholds (num_slices - 1 of them)
+  unsigned long long *sel_lookback = nullptr;   // selection chains, one per slice
   uint8_t *tile_state = nullptr;   // one block, zeroed per frame: TileState arrays
   TileState ts{};                  // per tile / per part: every pixel has stopped
   int blend_split = 1;             // K5 CTAs per semantic tile
@@ -149,41 +152,36 @@ int alloc_sort(gsplat_ctx *ctx, SortBuffers &s, size_t capacity) {
 
 int ceil_log2(uint32_t v) { int b = 0; while ((1u << b) < v) ++b; return b; }
 
-// Depth slices: cumulative fractions of the depth order at which the frame is cut.  The first
-// slice is small (dense tiles saturate within their first few thousand Gaussians: 1/16 of the
-// depth order with the default two slices), further cuts are spaced geometrically up to 1;
-// boundaries fall on K2 chunks.  depth_slices == 1: one slice (every tile's list
-// complete, the reference's lists).  GSPLAT_SLICE_FRACTIONS="f0,f1,...,1" overrides (experiments).
+// Depth slices: cumulative fractions of the drawn Gaussians (nearest first) at which the frame is
+// cut.  The first slice is small (dense tiles saturate within their first few thousand Gaussians:
+// 1/16 with the default two slices), further cuts are spaced geometrically up to 1.
+// depth_slices == 1: one slice (every tile's list complete, the reference's lists).  Scenes too
+// small to be worth cutting get one slice.  GSPLAT_SLICE_FRACTIONS="f0,f1,..." overrides
+// (experiments; the last slice always ends at 1).
 void plan_slices(gsplat_ctx *ctx) {
   const uint32_t n = ctx->scene.n;
   int want = ctx->cfg.depth_slices ? ctx->cfg.depth_slices : GSPLAT_DEFAULT_DEPTH_SLICES;
+  if (!ctx->cfg.depth_slices && n < 65536) want = 1;
   double frac[MAX_SLICES];
   for (int s = 0; s < want; ++s) frac[s] = std::pow(0.0625, (double)(want - 1 - s) / (want > 2 ? 0.5 * (want - 1) : 1.0));
   if (const char *e = std::getenv("GSPLAT_SLICE_FRACTIONS")) {
     if (!ctx->cfg.depth_slices) {
       int k = 0;
       const char *q = e;
-      while (*q && k < MAX_SLICES) {
+      while (*q && k < MAX_SLICES - 1) {
         char *end = nullptr;
         const double v = std::strtod(q, &end);
         if (end == q) break;
-        frac[k++] = v;
+        if (v > 0.0 && v < 1.0) frac[k++] = v;
         q = *end == ',' ? end + 1 : end;
       }
-      if (k) { want = k; frac[k - 1] = 1.0; }
+      want = k + 1;
+      frac[k] = 1.0;
     }
   }
-  int ns = 0;
-  uint32_t last = 0;
-  ctx->slice_begin[0] = 0;
-  for (int s = 0; s + 1 < want; ++s) {
-    uint64_t b = (uint64_t)((double)n * frac[s]);
-    b = (b + K2_CHUNK - 1) / K2_CHUNK * K2_CHUNK;
-    if (b >= n) break;
-    if (b > last) { ctx->slice_begin[++ns] = (uint32_t)b; last = (uint32_t)b; }
-  }
-  ctx->slice_begin[++ns] = n;
-  ctx->num_slices = ns;
+  ctx->num_slices = want;
+  ctx->slice_fr.count = want - 1;
+  for (int s = 0; s + 1 < want; ++s) ctx->slice_fr.f[s] = (float)frac[s];
 }
 
 // glm type_mat4x4.inl:630-648, left-to-right sums; column-major 16-float arrays
@@ -219,9 +217,10 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
   dfree(ctx->proj.rec); dfree(ctx->proj.rect);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->d_scalars); dfree(ctx->lookback);
+  dfree(ctx->sel_lookback); dfree(ctx->proj.depth_key);
   free_sort(ctx->sort_a); free_sort(ctx->sort_b);
   dfree(ctx->ranges); dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
-  dfree(ctx->count_diff); dfree(ctx->tile_state); dfree(ctx->tstate);
+  dfree(ctx->count_diff); dfree(ctx->live_sat); dfree(ctx->tile_state); dfree(ctx->tstate);
   if (ctx->copy_st) cudaStreamSynchronize(ctx->copy_st);
   for (auto &ss : ctx->sslots) {
     dfree(ss.d_bgr); dfree(ss.d_counts);
@@ -313,6 +312,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   CUC(cudaMemset(ctx->ranges, 0, sizeof(uint2) * ctx->num_tiles));
   {
     const size_t grid = (size_t)(ctx->tiles_across + 1) * (ctx->tiles_down + 1);
+    CUC(cudaMalloc(&ctx->live_sat, sizeof(uint32_t) * grid));
     CUC(cudaMalloc(&ctx->count_diff, sizeof(int) * grid));
     CUC(cudaMemset(ctx->count_diff, 0, sizeof(int) * grid));
     const size_t tsb = tile_state_bytes(ctx->num_tiles);
@@ -342,6 +342,7 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   for (auto &sl : ctx->slots) sl.pending = false;
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
   dfree(ctx->proj.rec); dfree(ctx->proj.rect); dfree(ctx->lookback);
+  dfree(ctx->sel_lookback); dfree(ctx->proj.depth_key);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4);
   ctx->have_scene = ctx->have_frame = false;
   const size_t na = n ? n : 1;
@@ -355,15 +356,17 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   CU(cudaMalloc(&ctx->proj.rect, na * sizeof(uint2)));
   ctx->n_blocks = (uint32_t)((n + K2_CHUNK - 1) / K2_CHUNK);
   CU(cudaMalloc(&ctx->lookback, (size_t)MAX_SLICES * (ctx->n_blocks + 1) * sizeof(unsigned long long)));
+  ctx->n_sel_blocks = (uint32_t)((n + 4095) / 4096);
+  CU(cudaMalloc(&ctx->sel_lookback, (size_t)MAX_SLICES * (ctx->n_sel_blocks + 1) * sizeof(unsigned long long)));
+  CU(cudaMalloc(&ctx->proj.depth_key, na * sizeof(uint32_t)));
   plan_slices(ctx);
   if (ctx->cfg.debug_records) {
     CU(cudaMalloc(&ctx->dbg_rec8, na * 8 * sizeof(float)));
     CU(cudaMalloc(&ctx->dbg_rect4, na * 4 * sizeof(int32_t)));
   }
-  {  // sort A holds one (depth key, index) pair per Gaussian; K1 writes its keys directly
+  {  // sort A holds the (depth key, index) pairs of the Gaussians selected for a slice: up to n
     int rc = alloc_sort(ctx, ctx->sort_a, n);
     if (rc) return rc;
-    ctx->proj.depth_key = ctx->sort_a.keys[0];
     const uint32_t n32 = (uint32_t)n;
     CU(cudaMemcpyAsync(ctx->d_scalars + SC_N, &n32, 4, cudaMemcpyHostToDevice, ctx->st));
     CU(cudaStreamSynchronize(ctx->st));

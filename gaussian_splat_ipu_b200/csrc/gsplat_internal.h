@@ -40,7 +40,7 @@ struct SceneSoA {
 //               the row pair is already clamped to this context's tile-row band)
 struct Projected {
   float4 *rec;
-  uint32_t *depth_key;   // ~bits(clip z) for drawn Gaussians (z < 0  =>  key < 2^31)
+  uint32_t *depth_key;   // ~bits(clip z) for drawn Gaussians (z < 0  =>  key < 2^31), per Gaussian
   uint2 *rect;           // {c0 | c1<<16, r0 | r1<<16} again, compact (8 B): K2 gathers it in depth
                          // order, and a random 8 B read costs one 32 B sector instead of a 48 B record
 };
@@ -79,11 +79,26 @@ void sort_plan(int nbits, int &passes, int &bits_per_pass);
 int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,
                       bool identity_vals, cudaStream_t st);
 
-// K2: walks positions [begin, end) of the DEPTH order (sorted_gauss = values of sort A) and emits
-// one (tile id, Gaussian index) pair per tile of each drawn Gaussian's rectangle — skipping tiles
-// whose tile_done flag is set when tile_done != nullptr (depth slices, duplicate.cu).  Offsets come
-// from a single-pass chained scan (decoupled look-back over `lookback`, which must be zeroed —
-// together with *ticket — before each launch), so the output is in (depth, gid, tile) order and
+// Depth-slice selection (select.cu).  tau[s] = depth-key quantile at fractions f[s] of the drawn
+// Gaussians (sampled); launch_select compacts, in index order, the (key, index) pairs of the
+// Gaussians with *tau_lo <= key < *tau_hi (nullptr = open end) whose rectangle covers a tile that
+// is still being blended (tile_done != nullptr), and writes their number to *total_out.
+// `lookback` (ceil(n / 4096) + 1 words) and *ticket must be zero on entry.
+struct SliceFractions {
+  int count;
+  float f[7];
+};
+void launch_depth_quantiles(const uint32_t *depth_key, uint32_t n, const SliceFractions &fr, uint32_t *tau,
+                            cudaStream_t st);
+void launch_select(const Projected &p, uint32_t n, const uint32_t *tau_lo, const uint32_t *tau_hi, int tiles_across,
+                   const uint32_t *live_sat, uint32_t *keys_out, uint32_t *idx_out, unsigned long long *lookback,
+                   uint32_t *ticket, uint32_t *total_out, cudaStream_t st);
+
+// K2: walks the *d_count (<= count_cap) depth-sorted Gaussians of one slice (sorted_gauss = values
+// of sort A) and emits one (tile id, Gaussian index) pair per tile of each Gaussian's rectangle —
+// skipping tiles whose tile_done flag is set when tile_done != nullptr.  Offsets come from a
+// single-pass chained scan (decoupled look-back over `lookback`, which must be zeroed — together
+// with *ticket — before each launch), so the output is in (depth, gid, tile) order and
 // bit-reproducible.  Writes the number of pairs to *total; sets *overflow (and writes nothing past
 // the buffer) if it exceeds capacity.
 constexpr int K2_THREADS = 256;
@@ -91,10 +106,19 @@ constexpr int K2_ITEMS = 4;
 constexpr int K2_LOG_CHUNK = 10;
 constexpr int K2_CHUNK = K2_THREADS * K2_ITEMS;   // Gaussians per CTA == per chain link
 static_assert((1 << K2_LOG_CHUNK) == K2_CHUNK, "binary search depth");
-void launch_duplicate(const Projected &p, const uint32_t *sorted_keys, const uint32_t *sorted_gauss, uint32_t begin,
-                      uint32_t end, int tiles_across, const uint8_t *tile_done, uint32_t *keys, uint32_t *vals,
+void launch_duplicate(const Projected &p, const uint32_t *sorted_gauss, const uint32_t *d_count, uint32_t count_cap,
+                      int tiles_across, const uint8_t *tile_done, const uint32_t *live_sat, uint32_t *keys, uint32_t *vals,
                       uint32_t capacity, unsigned long long *lookback, uint32_t *ticket, uint32_t *total,
                       uint32_t *overflow, cudaStream_t st);
+// Summed-area table over the tiles whose tile_done flag is clear ((tiles_down+1) x (tiles_across+1)
+// words) and the query used by the later depth slices: live tiles inside a tile rectangle.
+void launch_live_sat(const uint8_t *tile_done, int tiles_across, int tiles_down, uint32_t *sat, cudaStream_t st);
+__device__ __forceinline__ uint32_t live_tiles_in_rect(const uint32_t *__restrict__ sat, int tiles_across, uint32_t c0,
+                                                       uint32_t c1, uint32_t r0, uint32_t r1) {
+  const uint32_t gw = (uint32_t)tiles_across + 1u;
+  return (__ldg(&sat[(r1 + 1) * gw + c1 + 1]) - __ldg(&sat[r0 * gw + c1 + 1])) -
+         (__ldg(&sat[(r1 + 1) * gw + c0]) - __ldg(&sat[r0 * gw + c0]));
+}
 // a11: counts[tile] = drawn Gaussians whose rectangle covers the tile (the reference's list length).
 // `diff` is a (tiles_down+1) x (tiles_across+1) int grid that must be zero on entry and is left zero.
 constexpr size_t TILE_COUNT_MAX_SMEM = 200 * 1024;

@@ -74,6 +74,7 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
     const float4 p = __ldg(&s.pos_s0[i]);
     const bool live = (p.x == p.x);   // empty slots (gid <= 0, codelets.cpp:456) carry a NaN position
     int c0 = 0, c1 = -1, r0 = 0, r1 = -1;
+    uint2 rect_out = make_uint2(RECT_EMPTY, RECT_EMPTY);
     float px = 0.f, py = 0.f, cz = 0.f, cova = 0.f, covb = 0.f, covc = 0.f, rad = 0.f;
     bool drawn = false;
     if (live) {
@@ -175,14 +176,14 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
           r[1] = make_float4(kz, kw, col.x, col.y);
           r[2] = make_float4(col.z, cz, __uint_as_float((uint32_t)c0 | ((uint32_t)c1 << 16)),
                              __uint_as_float((uint32_t)e0 | ((uint32_t)e1 << 16)));
-          out.rect[i] = make_uint2((uint32_t)c0 | ((uint32_t)c1 << 16), (uint32_t)e0 | ((uint32_t)e1 << 16));
+          rect_out = make_uint2((uint32_t)c0 | ((uint32_t)c1 << 16), (uint32_t)e0 | ((uint32_t)e1 << 16));
         }
       }
     }
     // depth key: drawn Gaussians have clip z < 0 (codelets.cpp:493); ascending z (:314) ==
     // descending magnitude == ascending ~bits(z); everything else sorts last
     out.depth_key[i] = touched ? ~__float_as_uint(cz) : DEPTH_KEY_CULLED;
-    if (!touched) out.rect[i] = make_uint2(RECT_EMPTY, RECT_EMPTY);   // c0 > c1: covers no tile
+    out.rect[i] = rect_out;   // RECT_EMPTY (c0 > c1: covers no tile) unless the Gaussian is drawn
     if (dbg_rec8) {
       float4 *d = reinterpret_cast<float4 *>(dbg_rec8 + (size_t)i * 8);
       d[0] = make_float4(px, py, cz, cova);

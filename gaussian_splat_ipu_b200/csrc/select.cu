@@ -1,0 +1,206 @@
+// select.cu — depth-slice selection: which Gaussians enter sort A / K2 in each depth slice.
+//
+// K5 stops a pixel at the first Gaussian that would push its transmittance under 1e-4
+// (codelets/splat/codelets.cpp:405-408), so once every pixel of a tile has stopped nothing further
+// down the tile's z-ordered list (sortBuffer, codelets.cpp:303-356) can change the image.  The
+// frame is therefore processed in a few slices of increasing depth.  Slice s takes the Gaussians
+// whose depth key lies in [tau[s-1], tau[s]) — and, from the second slice on, whose rectangle
+// still covers a tile that has not stopped — sorts only those by depth, bins and blends them, and
+// K5 raises tile_done for tiles that stopped.  Every tile's list is an exact prefix of the
+// reference's list (complete unless the tile stopped), so the framebuffer is bit-identical to the
+// one-slice run, while the bulk of a dense scene — Gaussians buried behind saturated tiles — is
+// never sorted or duplicated at all.
+//
+// The thresholds tau are depth-key quantiles of a strided sample of this frame's keys: ANY
+// thresholds give the same image (they only decide where the slices are cut), so an approximate
+// quantile is enough and no state is carried from frame to frame.
+#include "gsplat_internal.h"
+
+namespace gsplat {
+
+// ---- thresholds: quantiles of a 4096-key sample, one CTA ----------------------------------------
+// fractions[s] (s < nthr) -> tau[s] = largest key value with (sample keys below it) <= fraction *
+// (drawn sample keys); found bit by bit (32 counting rounds over the register-resident sample).
+constexpr int QS_THREADS = 1024;
+constexpr int QS_PER_THREAD = 4;
+constexpr int QS_SAMPLE = QS_THREADS * QS_PER_THREAD;
+
+__global__ void __launch_bounds__(QS_THREADS)
+depth_quantile_kernel(const uint32_t *__restrict__ depth_key, uint32_t n, SliceFractions fr, uint32_t *__restrict__ tau) {
+  __shared__ uint32_t warp_cnt[QS_THREADS / 32];
+  __shared__ uint32_t total_s;
+  const uint32_t tid = threadIdx.x;
+  uint32_t key[QS_PER_THREAD];
+#pragma unroll
+  for (int k = 0; k < QS_PER_THREAD; ++k) {
+    const uint32_t j = tid * QS_PER_THREAD + k;
+    const uint64_t i = n > QS_SAMPLE ? (uint64_t)j * n / QS_SAMPLE : j;
+    key[k] = i < n ? depth_key[i] : DEPTH_KEY_CULLED;
+  }
+  auto count_below = [&](uint32_t bound) {   // sample keys < bound, over the CTA
+    uint32_t c = 0;
+#pragma unroll
+    for (int k = 0; k < QS_PER_THREAD; ++k) c += key[k] < bound ? 1u : 0u;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((tid & 31) == 0) warp_cnt[tid >> 5] = c;
+    __syncthreads();
+    if (tid < 32) {
+      const uint32_t t = __reduce_add_sync(0xffffffffu, warp_cnt[tid]);
+      if (tid == 0) total_s = t;
+    }
+    __syncthreads();
+    return total_s;
+  };
+  const uint32_t drawn = count_below(DEPTH_KEY_CULLED);
+  for (int s = 0; s < fr.count; ++s) {
+    const uint32_t target = (uint32_t)((double)drawn * fr.f[s]);
+    uint32_t t = 0;
+    for (int bit = 31; bit >= 0; --bit) {
+      const uint32_t cand = t | (1u << bit);
+      if (count_below(cand) <= target) t = cand;
+    }
+    if (tid == 0) tau[s] = t;
+  }
+}
+
+void launch_depth_quantiles(const uint32_t *depth_key, uint32_t n, const SliceFractions &fr, uint32_t *tau,
+                            cudaStream_t st) {
+  if (!fr.count) return;
+  ++g_launches;
+  depth_quantile_kernel<<<1, QS_THREADS, 0, st>>>(depth_key, n, fr, tau);
+}
+
+// ---- order-preserving selection (stream compaction with a chained scan) ---------------------------
+// One CTA = SEL_CHUNK consecutive Gaussians, blocked (thread t owns SEL_ITEMS consecutive ones), so
+// the selected (key, index) pairs come out in index order: the stable sort that follows then
+// breaks depth ties by gid exactly as the one-slice path does.
+constexpr int SEL_THREADS = 256;
+constexpr int SEL_ITEMS = 16;
+constexpr int SEL_CHUNK = SEL_THREADS * SEL_ITEMS;
+constexpr unsigned long long SLB_AGG = 1ull << 62, SLB_PREFIX = 2ull << 62, SLB_VALUE = (1ull << 62) - 1;
+
+__device__ __forceinline__ unsigned long long sel_ld(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sel_st(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+template <bool CHECK_DONE>
+__global__ void __launch_bounds__(SEL_THREADS)
+select_kernel(const uint32_t *__restrict__ depth_key, const uint2 *__restrict__ rect, uint32_t n,
+              const uint32_t *__restrict__ tau_lo /* nullptr: 0 */, const uint32_t *__restrict__ tau_hi /* nullptr: all drawn */,
+              int tiles_across, const uint32_t *__restrict__ live_sat, uint32_t *__restrict__ keys_out,
+              uint32_t *__restrict__ idx_out, unsigned long long *__restrict__ lookback, uint32_t *__restrict__ ticket,
+              uint32_t *__restrict__ total_out) {
+  __shared__ uint32_t wt[SEL_THREADS / 32 + 1];
+  __shared__ uint32_t chain_s;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) chain_s = atomicAdd(ticket, 1u);
+  __syncthreads();
+  const uint32_t b = chain_s;
+  const uint32_t lo = tau_lo ? *tau_lo : 0u, hi = tau_hi ? *tau_hi : DEPTH_KEY_CULLED;
+  const uint32_t first = b * SEL_CHUNK + tid * SEL_ITEMS;
+  uint32_t key[SEL_ITEMS];
+  if (first + SEL_ITEMS <= n) {
+    const uint4 *p = reinterpret_cast<const uint4 *>(depth_key + first);
+#pragma unroll
+    for (int q = 0; q < SEL_ITEMS / 4; ++q) {
+      const uint4 v = p[q];
+      key[q * 4 + 0] = v.x; key[q * 4 + 1] = v.y; key[q * 4 + 2] = v.z; key[q * 4 + 3] = v.w;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < SEL_ITEMS; ++k) key[k] = first + k < n ? depth_key[first + k] : DEPTH_KEY_CULLED;
+  }
+  uint32_t sel = 0;   // bit k: item k is selected
+#pragma unroll
+  for (int k = 0; k < SEL_ITEMS; ++k) {
+    bool take = key[k] >= lo && key[k] < hi;   // hi <= DEPTH_KEY_CULLED: culled Gaussians never pass
+    if (CHECK_DONE && take) {   // keep it only if its rectangle still covers a tile that is being blended
+      const uint2 rc = rect[first + k];
+      take = live_tiles_in_rect(live_sat, tiles_across, rc.x & 0xffffu, rc.x >> 16, rc.y & 0xffffu, rc.y >> 16) != 0;
+    }
+    sel |= take ? (1u << k) : 0u;
+  }
+  const uint32_t cnt = __popc(sel);
+  // exclusive scan over the CTA
+  uint32_t inc = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) wt[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t t = lane < SEL_THREADS / 32 ? wt[lane] : 0, ti = t;
+#pragma unroll
+    for (int o = 1; o < SEL_THREADS / 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, ti, o);
+      if (lane >= o) ti += u;
+    }
+    if (lane < SEL_THREADS / 32) wt[lane] = ti - t;
+    if (lane == SEL_THREADS / 32 - 1) wt[SEL_THREADS / 32] = ti;
+  }
+  __syncthreads();
+  const uint32_t total = wt[SEL_THREADS / 32];
+  uint32_t at = wt[warp] + inc - cnt;
+  // chained scan over CTAs (same scheme as K2's)
+  if (warp == 0) {
+    unsigned long long excl = 0;
+    if (b == 0) {
+      if (lane == 0) sel_st(&lookback[0], SLB_PREFIX | total);
+    } else {
+      if (lane == 0) sel_st(&lookback[b], SLB_AGG | total);
+      int pos = (int)b - 1;
+      while (true) {
+        const int q = pos - (int)lane;
+        unsigned long long w = SLB_PREFIX;
+        if (q >= 0) {
+          do { w = sel_ld(&lookback[q]); } while ((w >> 62) == 0);
+        }
+        const uint32_t is_prefix = __ballot_sync(0xffffffffu, (w >> 62) == 2);
+        const int firstp = is_prefix ? __ffs(is_prefix) - 1 : 32;
+        unsigned long long v = (int)lane <= firstp ? (w & SLB_VALUE) : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        excl += v;
+        if (is_prefix) break;
+        pos -= 32;
+      }
+      if (lane == 0) sel_st(&lookback[b], SLB_PREFIX | (excl + total));
+    }
+    if (lane == 0) {
+      chain_s = (uint32_t)excl;
+      if (b == gridDim.x - 1) *total_out = (uint32_t)(excl + total);
+    }
+  }
+  __syncthreads();
+  at += chain_s;
+#pragma unroll
+  for (int k = 0; k < SEL_ITEMS; ++k)
+    if (sel >> k & 1u) {
+      keys_out[at] = key[k];
+      idx_out[at] = first + k;
+      ++at;
+    }
+}
+
+void launch_select(const Projected &p, uint32_t n, const uint32_t *tau_lo, const uint32_t *tau_hi, int tiles_across,
+                   const uint32_t *live_sat, uint32_t *keys_out, uint32_t *idx_out, unsigned long long *lookback,
+                   uint32_t *ticket, uint32_t *total_out, cudaStream_t st) {
+  if (!n) return;
+  ++g_launches;
+  const int grid = ceil_div(n, SEL_CHUNK);
+  if (live_sat)
+    select_kernel<true><<<grid, SEL_THREADS, 0, st>>>(p.depth_key, p.rect, n, tau_lo, tau_hi, tiles_across, live_sat,
+                                                      keys_out, idx_out, lookback, ticket, total_out);
+  else
+    select_kernel<false><<<grid, SEL_THREADS, 0, st>>>(p.depth_key, p.rect, n, tau_lo, tau_hi, tiles_across, nullptr,
+                                                       keys_out, idx_out, lookback, ticket, total_out);
+}
+
+}  // namespace gsplat

@@ -40,7 +40,7 @@ class FrameStats(C.Structure):
     _fields_ = [("num_gaussians", C.c_uint64), ("num_drawn", C.c_uint64), ("num_duplicates", C.c_uint64),
                 ("dup_capacity", C.c_uint64), ("max_tile_count", C.c_uint32), ("num_tiles", C.c_uint32),
                 ("regrown", C.c_uint32), ("key_bits", C.c_uint32), ("num_reference_duplicates", C.c_uint64),
-                ("depth_slices", C.c_uint32), ("reserved", C.c_uint32)]
+                ("depth_slices", C.c_uint32), ("num_depth_sorted", C.c_uint32)]
 
 
 # every symbol include/gsplat_b200.h declares: name -> (restype, argtypes)

@@ -56,9 +56,10 @@ typedef struct gsplat_config {
   int debug_records;     /* K1 also writes the projected records for gsplat_read_projected    */
   size_t dup_capacity;   /* initial capacity of the (tile,Gaussian) duplicate buffers;        */
                          /* 0 = choose from the scene size; grows on demand                   */
-  int depth_slices;      /* the frame is binned and blended in this many slices of the depth  */
-                         /* order, nearest first; tiles whose pixels have all stopped          */
-                         /* (test_T < 1e-4, codelets.cpp:405-408) drop out of the later slices. */
+  int depth_slices;      /* the frame is sorted, binned and blended in this many slices of     */
+                         /* increasing depth; tiles whose pixels have all stopped (test_T <    */
+                         /* 1e-4, codelets.cpp:405-408) drop out of the later slices, and so do */
+                         /* the Gaussians that only cover such tiles.                           */
                          /* 1 = one slice: every tile's list is the reference's complete list.  */
                          /* 0 = default (GSPLAT_DEFAULT_DEPTH_SLICES).  Framebuffer and counts   */
                          /* do not depend on it; lists are exact prefixes of the reference's.   */
@@ -149,7 +150,7 @@ typedef struct gsplat_frame_stats {
   uint32_t key_bits;      /* sorted key width: 32 depth bits + tile-id bits */
   uint64_t num_reference_duplicates; /* sum of the per-tile counts = D of the reference's lists */
   uint32_t depth_slices;  /* slices the frame was cut into                   */
-  uint32_t reserved;
+  uint32_t num_depth_sorted; /* Gaussians that entered a depth sort (sort A), all slices */
 } gsplat_frame_stats;
 int gsplat_get_frame_stats(gsplat_ctx *ctx, gsplat_frame_stats *out);
 
