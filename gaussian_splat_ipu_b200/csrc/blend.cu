@@ -52,7 +52,8 @@ template <bool COUNT, bool FIRST, bool LAST>
 __global__ void __launch_bounds__(BLEND_MAX_ROWS * 32)
 blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
              int tiles_across, int row_begin, int full_tile_h, int tile_h, float4 *__restrict__ fb,
-             float *__restrict__ tstate, TileState ts, unsigned long long *__restrict__ pair_counters) {
+             float *__restrict__ tstate, TileState ts, const uint32_t *__restrict__ order,
+             unsigned long long *__restrict__ pair_counters) {
   extern __shared__ __align__(16) unsigned char blend_smem_raw[];
   const long long t_begin = COUNT ? clock64() : 0;
   const uint32_t tid = threadIdx.x, lane = tid & 31, row = tid >> 5;
@@ -65,7 +66,8 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   // of it so that a crowded tile's list is walked by several SMs at once); parts of one tile are
   // neighbours in the grid
   const uint32_t nsub = (uint32_t)(full_tile_h / tile_h), sub = blockIdx.x % nsub;
-  const uint32_t tile = blockIdx.x / nsub + (uint32_t)row_begin * tiles_across;
+  // tiles are taken longest list first (tile_order_kernel) so the long ones do not start last
+  const uint32_t tile = order[blockIdx.x / nsub] + (uint32_t)row_begin * tiles_across;
   const uint2 range = ranges[tile];
   const uint32_t n = range.y - range.x;
   const uint32_t part = tile * nsub + sub;
@@ -195,9 +197,55 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   fb[px] = make_float4(Cr, Cg, Cb, Ca);
 }
 
+// ---- launch order of the tiles: longest list first ---------------------------------------------
+// CTAs are dispatched in blockIdx order; a tile with a long list that starts late leaves the other
+// SMs idle at the end of the launch.  One CTA buckets the band's tiles by list length (power-of-two
+// class + 2 mantissa bits, longest class first; tiles that already stopped count as empty) and
+// writes the permutation K5 indexes with blockIdx.  Order inside a class is arbitrary: it only
+// changes scheduling, never results.
+constexpr int ORDER_BUCKETS = 33 * 4;
+__device__ __forceinline__ uint32_t order_bucket(uint32_t len) {
+  if (len == 0) return ORDER_BUCKETS - 1;
+  const uint32_t e = 31u - (uint32_t)__clz(len);                       // floor(log2 len)
+  const uint32_t m = e >= 2 ? (len >> (e - 2)) & 3u : (len << (2 - e)) & 3u;
+  return (31u - e) * 4u + (3u - m);                                     // longer lists -> smaller bucket
+}
+__global__ void __launch_bounds__(1024)
+tile_order_kernel(const uint2 *__restrict__ ranges, int tiles_across, int row_begin, int ntiles,
+                  const uint8_t *__restrict__ tile_done, uint32_t *__restrict__ order) {
+  __shared__ uint32_t cnt[ORDER_BUCKETS];
+  for (int k = threadIdx.x; k < ORDER_BUCKETS; k += blockDim.x) cnt[k] = 0;
+  __syncthreads();
+  const uint32_t t0 = (uint32_t)row_begin * tiles_across;
+  for (int i = threadIdx.x; i < ntiles; i += blockDim.x) {
+    const uint2 r = ranges[t0 + i];
+    const uint32_t len = (tile_done && tile_done[t0 + i]) ? 0u : r.y - r.x;
+    atomicAdd(&cnt[order_bucket(len)], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int k = 0; k < ORDER_BUCKETS; ++k) { const uint32_t c = cnt[k]; cnt[k] = run; run += c; }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < ntiles; i += blockDim.x) {
+    const uint2 r = ranges[t0 + i];
+    const uint32_t len = (tile_done && tile_done[t0 + i]) ? 0u : r.y - r.x;
+    order[atomicAdd(&cnt[order_bucket(len)], 1u)] = (uint32_t)i;
+  }
+}
+
+static void launch_tile_order(const uint2 *ranges, const FrameParams &fp, const uint8_t *tile_done, bool first,
+                              uint32_t *order, cudaStream_t st) {
+  const int ntiles = (fp.row_end - fp.row_begin) * fp.tiles_across;
+  if (ntiles <= 0) return;
+  ++g_launches;
+  tile_order_kernel<<<1, 1024, 0, st>>>(ranges, fp.tiles_across, fp.row_begin, ntiles, first ? nullptr : tile_done, order);
+}
+
 template <bool COUNT, bool FIRST, bool LAST>
 static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                           float4 *fb_tiled, float *tstate, const TileState &ts, int split,
+                           float4 *fb_tiled, float *tstate, const TileState &ts, int split, const uint32_t *order,
                            unsigned long long *pair_counters, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
@@ -213,13 +261,14 @@ static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, cons
   const size_t smem = (size_t)tile_h * 32 * BLEND_SMEM_PER_THREAD;
   ++g_launches;
   blend_kernel<COUNT, FIRST, LAST><<<rows * fp.tiles_across * split, tile_h * 32, smem, st>>>(
-      p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, full_h, tile_h, fb_tiled, tstate, ts, pair_counters);
+      p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, full_h, tile_h, fb_tiled, tstate, ts, order, pair_counters);
 }
 
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                  float4 *fb_tiled, float *tstate, const TileState &ts, int split, bool first, bool last,
-                  unsigned long long *pair_counters, cudaStream_t st) {
-#define GSPLAT_BLEND(C, F, L) launch_blend_t<C, F, L>(p, sorted_vals, ranges, fp, fb_tiled, tstate, ts, split, pair_counters, st)
+                  float4 *fb_tiled, float *tstate, const TileState &ts, int split, uint32_t *order, bool first,
+                  bool last, unsigned long long *pair_counters, cudaStream_t st) {
+  launch_tile_order(ranges, fp, ts.tile_done, first, order, st);
+#define GSPLAT_BLEND(C, F, L) launch_blend_t<C, F, L>(p, sorted_vals, ranges, fp, fb_tiled, tstate, ts, split, order, pair_counters, st)
   if (pair_counters) {
     if (first) { if (last) GSPLAT_BLEND(true, true, true); else GSPLAT_BLEND(true, true, false); }
     else { if (last) GSPLAT_BLEND(true, false, true); else GSPLAT_BLEND(true, false, false); }

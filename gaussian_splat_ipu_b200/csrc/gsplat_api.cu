@@ -76,6 +76,7 @@ struct gsplat_ctx {
   uint2 *ranges = nullptr;
   uint32_t *counts = nullptr;      // a11: reference list length of every tile (tile_count_kernel)
   int *count_diff = nullptr;       // difference grid of tile_count_kernel (kept zero between frames)
+  uint32_t *tile_order = nullptr;  // K5 launch order of the tiles (longest list first), per slice
   uint32_t *live_sat = nullptr;    // summed-area table of the tiles still being blended (depth slices)
   // depth slices (select.cu): slice s = depth keys in [tau[s-1], tau[s]), tau = sampled quantiles
   int num_slices = 1;
@@ -220,7 +221,7 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   dfree(ctx->sel_lookback); dfree(ctx->proj.depth_key);
   free_sort(ctx->sort_a); free_sort(ctx->sort_b);
   dfree(ctx->ranges); dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
-  dfree(ctx->count_diff); dfree(ctx->live_sat); dfree(ctx->tile_state); dfree(ctx->tstate);
+  dfree(ctx->count_diff); dfree(ctx->live_sat); dfree(ctx->tile_order); dfree(ctx->tile_state); dfree(ctx->tstate);
   if (ctx->copy_st) cudaStreamSynchronize(ctx->copy_st);
   for (auto &ss : ctx->sslots) {
     dfree(ss.d_bgr); dfree(ss.d_counts);
@@ -313,6 +314,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   {
     const size_t grid = (size_t)(ctx->tiles_across + 1) * (ctx->tiles_down + 1);
     CUC(cudaMalloc(&ctx->live_sat, sizeof(uint32_t) * grid));
+    CUC(cudaMalloc(&ctx->tile_order, sizeof(uint32_t) * ctx->num_tiles));
     CUC(cudaMalloc(&ctx->count_diff, sizeof(int) * grid));
     CUC(cudaMemset(ctx->count_diff, 0, sizeof(int) * grid));
     const size_t tsb = tile_state_bytes(ctx->num_tiles);

@@ -135,6 +135,8 @@ void launch_tile_ranges(const uint32_t *keys, const uint32_t *d_n, uint32_t n_up
 // pixels of the tile stopped).  pair_counters != nullptr selects the counting variant (roofline
 // accounting): [0] += visited pairs, [1] += blended pairs, then per tile {cycles, visited pairs}.
 // `split`: CTAs per semantic tile (each blends tile_h / split rows; must divide tile_h).
+// `order`: scratch of one word per tile; launch_blend fills it with the band's tiles, longest list
+// first, and K5 takes its tiles in that order.
 struct TileState {
   uint8_t *tile_done;    // [tiles] every pixel of the tile has stopped (read by K2 of later slices)
   uint8_t *part_done;    // [tiles * BLEND_MAX_SPLIT] every pixel of the part has stopped
@@ -143,8 +145,8 @@ struct TileState {
 constexpr int BLEND_MAX_SPLIT = 8;
 inline size_t tile_state_bytes(int tiles) { return (size_t)tiles * (1 + BLEND_MAX_SPLIT + 4) + 16; }
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                  float4 *fb_tiled, float *tstate, const TileState &ts, int split, bool first, bool last,
-                  unsigned long long *pair_counters, cudaStream_t st);
+                  float4 *fb_tiled, float *tstate, const TileState &ts, int split, uint32_t *order, bool first,
+                  bool last, unsigned long long *pair_counters, cudaStream_t st);
 
 // a10: tiled f32 RGBA -> de-tiled BGR8 rows.
 void launch_bgr8(const float4 *fb_tiled, uint8_t *bgr, int W, int H, int tile_w, int tile_h,
