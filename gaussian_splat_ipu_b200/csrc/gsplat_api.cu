@@ -58,6 +58,8 @@ enum Scalar { SC_V = 0, SC_OVERFLOW = 1, SC_TICKET0 = 8 /* K2 chain ticket per s
 struct gsplat_ctx {
   gsplat_config cfg{};
   cudaStream_t st = nullptr;
+  cudaStream_t aux_st = nullptr;            // per-tile counts run beside the slices (nothing in the frame reads them)
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   std::string err;
   int tiles_across = 0, tiles_down = 0, num_tiles = 0, tile_bits = 0;
   // scene
@@ -240,6 +242,9 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   if (ctx->t1) cudaEventDestroy(ctx->t1);
   if (ctx->post0) cudaEventDestroy(ctx->post0);
   if (ctx->post1) cudaEventDestroy(ctx->post1);
+  if (ctx->aux_st) { cudaStreamSynchronize(ctx->aux_st); cudaStreamDestroy(ctx->aux_st); }
+  if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+  if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
   if (ctx->st) cudaStreamDestroy(ctx->st);
   delete ctx;
 }
@@ -287,6 +292,9 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   } while (0)
   CUC(cudaSetDevice(cfg->device));
   CUC(cudaStreamCreateWithFlags(&ctx->st, cudaStreamNonBlocking));
+  CUC(cudaStreamCreateWithFlags(&ctx->aux_st, cudaStreamNonBlocking));
+  CUC(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+  CUC(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
   CUC(cudaHostAlloc(&ctx->h_scalars, NUM_SLOTS * SC_FRAME_WORDS * sizeof(uint32_t), cudaHostAllocDefault));
   for (int k = 0; k < NUM_SLOTS; ++k) {
     FrameSlot &sl = ctx->slots[k];

@@ -71,8 +71,8 @@ void launch_depth_quantiles(const uint32_t *depth_key, uint32_t n, const SliceFr
 }
 
 // ---- order-preserving selection (stream compaction with a chained scan) ---------------------------
-// One CTA = SEL_CHUNK consecutive Gaussians, blocked (thread t owns SEL_ITEMS consecutive ones), so
-// the selected (key, index) pairs come out in index order: the stable sort that follows then
+// One CTA = SEL_CHUNK consecutive Gaussians; positions come from warp ballots plus a scan of the
+// per-(item row, warp) counts, so the selected (key, index) pairs come out in index order: the stable sort that follows then
 // breaks depth ties by gid exactly as the one-slice path does.
 constexpr int SEL_THREADS = 256;
 constexpr int SEL_ITEMS = 16;
@@ -95,59 +95,55 @@ select_kernel(const uint32_t *__restrict__ depth_key, const uint2 *__restrict__ 
               int tiles_across, const uint32_t *__restrict__ live_sat, uint32_t *__restrict__ keys_out,
               uint32_t *__restrict__ idx_out, unsigned long long *__restrict__ lookback, uint32_t *__restrict__ ticket,
               uint32_t *__restrict__ total_out) {
-  __shared__ uint32_t wt[SEL_THREADS / 32 + 1];
+  __shared__ uint32_t wc[SEL_ITEMS * (SEL_THREADS / 32) + 1];
   __shared__ uint32_t chain_s;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) chain_s = atomicAdd(ticket, 1u);
   __syncthreads();
   const uint32_t b = chain_s;
   const uint32_t lo = tau_lo ? *tau_lo : 0u, hi = tau_hi ? *tau_hi : DEPTH_KEY_CULLED;
-  const uint32_t first = b * SEL_CHUNK + tid * SEL_ITEMS;
+  // striped: item k of thread tid is Gaussian base + k * SEL_THREADS + tid, so every load of a warp
+  // is one contiguous run; output order = (k, tid) = index order
+  const uint32_t base_i = b * SEL_CHUNK;
   uint32_t key[SEL_ITEMS];
-  if (first + SEL_ITEMS <= n) {
-    const uint4 *p = reinterpret_cast<const uint4 *>(depth_key + first);
 #pragma unroll
-    for (int q = 0; q < SEL_ITEMS / 4; ++q) {
-      const uint4 v = p[q];
-      key[q * 4 + 0] = v.x; key[q * 4 + 1] = v.y; key[q * 4 + 2] = v.z; key[q * 4 + 3] = v.w;
-    }
-  } else {
-#pragma unroll
-    for (int k = 0; k < SEL_ITEMS; ++k) key[k] = first + k < n ? depth_key[first + k] : DEPTH_KEY_CULLED;
+  for (int k = 0; k < SEL_ITEMS; ++k) {
+    const uint32_t i = base_i + k * SEL_THREADS + tid;
+    key[k] = i < n ? depth_key[i] : DEPTH_KEY_CULLED;
   }
   uint32_t sel = 0;   // bit k: item k is selected
 #pragma unroll
   for (int k = 0; k < SEL_ITEMS; ++k) {
     bool take = key[k] >= lo && key[k] < hi;   // hi <= DEPTH_KEY_CULLED: culled Gaussians never pass
     if (CHECK_DONE && take) {   // keep it only if its rectangle still covers a tile that is being blended
-      const uint2 rc = rect[first + k];
+      const uint2 rc = rect[base_i + k * SEL_THREADS + tid];
       take = live_tiles_in_rect(live_sat, tiles_across, rc.x & 0xffffu, rc.x >> 16, rc.y & 0xffffu, rc.y >> 16) != 0;
     }
     sel |= take ? (1u << k) : 0u;
+    const uint32_t m = __ballot_sync(0xffffffffu, take);
+    if (lane == 0) wc[k * (SEL_THREADS / 32) + warp] = __popc(m);
   }
-  const uint32_t cnt = __popc(sel);
-  // exclusive scan over the CTA
-  uint32_t inc = cnt;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += t;
-  }
-  if (lane == 31) wt[warp] = inc;
   __syncthreads();
+  // exclusive scan of the SEL_ITEMS x warps counts in (k, warp) order: one warp, 4 entries per lane
+  constexpr int NWC = SEL_ITEMS * (SEL_THREADS / 32);
+  static_assert(NWC == 128, "one warp scans 4 entries per lane");
   if (warp == 0) {
-    uint32_t t = lane < SEL_THREADS / 32 ? wt[lane] : 0, ti = t;
+    uint32_t v[4], sum = 0;
 #pragma unroll
-    for (int o = 1; o < SEL_THREADS / 32; o <<= 1) {
-      const uint32_t u = __shfl_up_sync(0xffffffffu, ti, o);
-      if (lane >= o) ti += u;
+    for (int q = 0; q < 4; ++q) { v[q] = wc[lane * 4 + q]; sum += v[q]; }
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
     }
-    if (lane < SEL_THREADS / 32) wt[lane] = ti - t;
-    if (lane == SEL_THREADS / 32 - 1) wt[SEL_THREADS / 32] = ti;
+    uint32_t run = inc - sum;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { wc[lane * 4 + q] = run; run += v[q]; }
+    if (lane == 31) wc[NWC] = inc;
   }
   __syncthreads();
-  const uint32_t total = wt[SEL_THREADS / 32];
-  uint32_t at = wt[warp] + inc - cnt;
+  const uint32_t total = wc[NWC];
   // chained scan over CTAs (same scheme as K2's)
   if (warp == 0) {
     unsigned long long excl = 0;
@@ -179,14 +175,17 @@ select_kernel(const uint32_t *__restrict__ depth_key, const uint2 *__restrict__ 
     }
   }
   __syncthreads();
-  at += chain_s;
+  const uint32_t cbase = chain_s;
 #pragma unroll
-  for (int k = 0; k < SEL_ITEMS; ++k)
-    if (sel >> k & 1u) {
+  for (int k = 0; k < SEL_ITEMS; ++k) {
+    const bool take = sel >> k & 1u;
+    const uint32_t m = __ballot_sync(0xffffffffu, take);
+    if (take) {
+      const uint32_t at = cbase + wc[k * (SEL_THREADS / 32) + warp] + __popc(m & ((1u << lane) - 1u));
       keys_out[at] = key[k];
-      idx_out[at] = first + k;
-      ++at;
+      idx_out[at] = base_i + k * SEL_THREADS + tid;
     }
+  }
 }
 
 void launch_select(const Projected &p, uint32_t n, const uint32_t *tau_lo, const uint32_t *tau_hi, int tiles_across,
