@@ -181,18 +181,25 @@ def reference_arm(args):
 
 
 def stage_rooflines(tm, st, pairs, blended, W, H, tiles, clocks_mhz, peaks):
-    """Per-stage achieved vs roofline from ALGORITHMIC bytes / flops."""
+    """Per-stage achieved vs roofline from ALGORITHMIC bytes / flops.
+    N Gaussians, V drawn, A = Gaussians that entered a depth sort (all slices), D = (tile, Gaussian)
+    pairs binned (all slices), S depth slices."""
     N, V, D = st.num_gaussians, st.num_drawn, st.num_duplicates
+    A, S = st.num_depth_sorted, max(1, st.depth_slices)
     tile_bits = st.key_bits - 32
-    pb = (tile_bits + 6) // 7                              # digits of sort B (sort A: 5 digits of 7/6 bits)
+    pb = (tile_bits + 6) // 7                              # digits of sort B (sort A: 5 digits of 7/.../4 bits)
     hbm = peaks["hbm_gbs"]
     mhz = clocks_mhz or peaks.get("sm_max_mhz", 1965.0)
     fp32_peak = 2 * 128 * 148 * mhz * 1e6 / 1e12          # TFLOP/s at the observed SM clock
-    # per digit: 4 B histogram read + 8 B read + 8 B write per element (first digit of sort A
-    # generates its values: 4 B less)
-    alg_bytes = {"k1_project": 56 * N + 48 * V + 4 * N, "k3a_sort_depth": (5 * 20 - 4) * N,
-                 "k2_duplicate": 8 * N + 16 * V + 8 * D, "k3b_sort_tile": 20 * pb * D,
-                 "k4_ranges": 4 * D + 8 * tiles}
+    alg_bytes = {
+        # scene SoA in, 48 B record per drawn Gaussian + key + rect per Gaussian out; rect re-read by the counts
+        "k1_project": 56 * N + 48 * V + 4 * N + 8 * N + 8 * N,
+        # per slice: keys read by the selection (+ rect from the 2nd slice on), selected pairs written;
+        # per digit 4 B histogram read + 8 B read + 8 B write per selected Gaussian
+        "k3a_sort_depth": 4 * N * S + 8 * N * (S - 1) + 8 * A + 5 * 20 * A,
+        "k2_duplicate": 4 * A + 8 * A + 8 * D,
+        "k3b_sort_tile": 20 * pb * D,
+        "k4_ranges": 4 * D + 8 * tiles * S}
     out = {}
     for k, b in alg_bytes.items():
         ms = tm[k]
@@ -329,6 +336,24 @@ def gpu_arm(args):
     r = stages[dom]
     roofline = {"kernel": dom, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
                 "frac": r["frac"], "traffic": None, "peak_source": peak_src, "ms": r["ms"]}
+    # the same frames with ONE depth slice (every tile's list complete, as the reference builds them):
+    # reported beside the headline so the effect of the slices is visible; a bounded number of steps
+    s.close()
+    s1 = B200Splatter(g, W, H, device=local, depth_slices=1)
+    s1.updateProjection(proj); s1.updateFocalLengths(FOV, SCALE_DIV)
+    K1 = min(K, 60)
+    for k in range(5):
+        s1.updateModelView(views[k % ORBIT_VIEWS]); s1.execute()
+    s1.sync()
+    s1.timer_begin()
+    for k in range(K1):
+        s1.updateModelView(views[((Wm + k) * world + rank) % ORBIT_VIEWS]); s1.execute()
+    one_ms = s1.timer_end()
+    st1 = s1.stats()
+    one_slice = {"value": K1 / (one_ms * 1e-3), "unit": "frames/s per GPU", "steps": K1,
+                 "duplicates": int(st1.num_duplicates), "depth_sorted": int(st1.num_depth_sorted),
+                 "note": "depth_slices=1: complete per-tile lists (bit-exact to the reference's), same framebuffer"}
+    s1.close()
     cpu = None
     if args.gpus == 1 and not args.no_cpu_baseline:
         from oracle import pyoracle
@@ -341,9 +366,13 @@ def gpu_arm(args):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "gaussians": n, "width": W, "height": H, "tile": "32x20",
                        "scale_div": SCALE_DIV, "views": f"orbit of {ORBIT_VIEWS}, one view per GPU per step",
+                       "depth_slices": "library default (2): lists are exact prefixes of the reference's, "
+                                       "framebuffer and counts identical to the one-slice run",
                        "l2": "inputs larger than L2 (scene + records > 126 MB) and a new camera every step"},
             "mgaussians_per_s": n * fps / 1e6, "device_ms_per_step": dev_ms_max / K,
             "frame": {"drawn": int(st.num_drawn), "duplicates": int(st.num_duplicates),
+                      "reference_duplicates": int(st.num_reference_duplicates),
+                      "depth_sorted": int(st.num_depth_sorted), "depth_slices": int(st.depth_slices),
                       "max_tile_count": int(st.max_tile_count), "pairs": pairs, "blended": blended},
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": 34 * 4,
                     "d2h_bytes_per_step": W * H * 3 + s.num_tiles * 4 + 12,
@@ -354,6 +383,7 @@ def gpu_arm(args):
                                    "api": "execute + getFrameBuffer + getIPUHistogram, one frame at a time",
                                    "d2h_bytes_per_step": W * H * 3 + s.num_tiles * 8 + 8}},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "stages": stages,
+            "one_slice": one_slice,
             "cpu_baseline": cpu}
     if args.stage_report:
         with open(args.stage_report, "w") as fh:

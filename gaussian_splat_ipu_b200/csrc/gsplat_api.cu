@@ -32,6 +32,8 @@ struct FrameSlot {
   cudaEvent_t done = nullptr;
   uint32_t *h = nullptr;   // pinned copy of the frame's device scalars (enum Scalar)
   int num_slices = 1;
+  cudaEvent_t t_begin = nullptr, t_end = nullptr;   // whole-frame device time (slice auto-tuning)
+  bool auto_timed = false;
   bool pending = false, timed = false, overflowed = false;
   uint64_t frame_no = 0;
 };
@@ -81,7 +83,17 @@ struct gsplat_ctx {
   uint32_t *tile_order = nullptr;  // K5 launch order of the tiles (longest list first), per slice
   uint32_t *live_sat = nullptr;    // summed-area table of the tiles still being blended (depth slices)
   // depth slices (select.cu): slice s = depth keys in [tau[s-1], tau[s]), tau = sampled quantiles
-  int num_slices = 1;
+  int num_slices = 1;              // slices of a sliced frame (plan_slices)
+  int frame_slices = 1;            // slices of the frame being / last enqueued
+  // depth_slices == 0: sliced and one-slice frames give the same image, so the context measures
+  // both (device time, smallest of the last four samples) and renders with the faster; every AUTO_PROBE-th frame
+  // re-measures the other
+  bool auto_slices = false;
+  double ema_ms[2] = {0, 0};       // [0] one slice  [1] sliced: current estimate (min of the last 4 samples)
+  float samples[2][4] = {{0}};
+  uint64_t nsamples[2] = {0, 0};
+  bool ema_valid[2] = {false, false};
+  uint64_t auto_frames = 0, mode_frames[2] = {0, 0};
   SliceFractions slice_fr{};       // cumulative fractions of the thresholds (num_slices - 1 of them)
   unsigned long long *sel_lookback = nullptr;   // selection chains, one per slice
   uint8_t *tile_state = nullptr;   // one block, zeroed per frame: TileState arrays
@@ -183,6 +195,11 @@ void plan_slices(gsplat_ctx *ctx) {
     }
   }
   ctx->num_slices = want;
+  ctx->frame_slices = want;
+  ctx->auto_slices = !ctx->cfg.depth_slices && want > 1 && !std::getenv("GSPLAT_SLICE_FRACTIONS");
+  ctx->ema_valid[0] = ctx->ema_valid[1] = false;
+  ctx->nsamples[0] = ctx->nsamples[1] = 0;
+  ctx->auto_frames = 0;
   ctx->slice_fr.count = want - 1;
   for (int s = 0; s + 1 < want; ++s) ctx->slice_fr.f[s] = (float)frac[s];
 }
@@ -215,6 +232,9 @@ const char *gsplat_last_error(const gsplat_ctx *ctx) { return ctx ? ctx->err.c_s
 
 void gsplat_destroy(gsplat_ctx *ctx) {
   if (!ctx) return;
+  if (std::getenv("GSPLAT_DEBUG"))
+    std::fprintf(stderr, "[gsplat] auto=%d frames one-slice %llu (%.3f ms) sliced %llu (%.3f ms)\n", (int)ctx->auto_slices,
+                 (unsigned long long)ctx->mode_frames[0], ctx->ema_ms[0], (unsigned long long)ctx->mode_frames[1], ctx->ema_ms[1]);
   cudaSetDevice(ctx->cfg.device);
   if (ctx->st) cudaStreamSynchronize(ctx->st);
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
@@ -237,6 +257,8 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   for (auto &sl : ctx->slots) {
     for (auto &e : sl.ev) if (e) cudaEventDestroy(e);
     if (sl.done) cudaEventDestroy(sl.done);
+    if (sl.t_begin) cudaEventDestroy(sl.t_begin);
+    if (sl.t_end) cudaEventDestroy(sl.t_end);
   }
   if (ctx->t0) cudaEventDestroy(ctx->t0);
   if (ctx->t1) cudaEventDestroy(ctx->t1);
@@ -300,6 +322,8 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     FrameSlot &sl = ctx->slots[k];
     for (auto &ev : sl.ev) CUC(cudaEventCreate(&ev));
     CUC(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    CUC(cudaEventCreate(&sl.t_begin));
+    CUC(cudaEventCreate(&sl.t_end));
     sl.h = ctx->h_scalars + SC_FRAME_WORDS * k;
   }
   CUC(cudaEventCreate(&ctx->t0));

@@ -73,11 +73,11 @@ constexpr int RS_ITEMS = 16;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
 constexpr int RS_MAX_BITS = 7;      // digit width limit of the counter-based ranking (128 digits)
 constexpr int RS_GRID = 148 * 3;   // CTAs walk RS_TILE-element tiles with a grid stride
-void sort_plan(int nbits, int &passes, int &bits_per_pass);
+void sort_plan(int nbits, int &passes, int &bits_per_pass, int max_bits = RS_MAX_BITS);
 // identity_vals: the first digit takes value = element index instead of reading vals[0].
 // returns index (0/1) of the buffer holding the sorted result
 int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,
-                      bool identity_vals, cudaStream_t st);
+                      bool identity_vals, cudaStream_t st, int max_bits = RS_MAX_BITS);
 
 // Depth-slice selection (select.cu).  tau[s] = depth-key quantile at fractions f[s] of the drawn
 // Gaussians (sampled); launch_select compacts, in index order, the (key, index) pairs of the

@@ -15,7 +15,8 @@
 // tiles -> ranked scatter.  "Tile" here = RS_TILE consecutive elements; CTAs walk tiles with a grid
 // stride and the element count is read on the device (*d_n), so the host never needs to know N or
 // D to launch the sort (no mid-frame synchronisation).  HBM-bound: 4 B (hist) + 8 B + 8 B (scatter)
-// per element per digit; digits are at most RS_MAX_BITS = 7 bits wide.
+// per element per digit; digits are at most 7 bits wide (8 for the small per-slice depth sorts,
+// whose 128 KB of counters leave one CTA per SM).
 #include "gsplat_internal.h"
 
 namespace gsplat {
@@ -217,9 +218,9 @@ rs_scan_kernel(uint32_t *__restrict__ block_hist, uint32_t stride, const uint32_
 
 // ---- stable ranked scatter ---------------------------------------------------------------------
 // Dynamic shared memory: the counter words, re-used as the (key, value) staging area once every
-// element knows its position; then out_base[128] and the scan scratch.
+// element knows its position; then out_base[256] and the scan scratch.
 struct RsTail {
-  uint32_t out_base[128];
+  uint32_t out_base[256];
   uint32_t wt[RS_WARPS + 1];
 };
 __host__ __device__ constexpr size_t rs_scatter_smem(int bits) {
@@ -311,9 +312,10 @@ rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restri
   }
 }
 
-void sort_plan(int nbits, int &passes, int &bits_per_pass) {
+void sort_plan(int nbits, int &passes, int &bits_per_pass, int max_bits) {
   if (nbits < 1) nbits = 1;
-  passes = (nbits + RS_MAX_BITS - 1) / RS_MAX_BITS;
+  if (max_bits < 1 || max_bits > 8) max_bits = RS_MAX_BITS;
+  passes = (nbits + max_bits - 1) / max_bits;
   bits_per_pass = (nbits + passes - 1) / passes;
 }
 
@@ -337,13 +339,13 @@ static void launch_pass(SortBuffers &sb, int cur, bool identity, const uint32_t 
 }
 
 int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,
-                      bool identity_vals, cudaStream_t st) {
+                      bool identity_vals, cudaStream_t st, int max_bits) {
   if (n_upper > sb.capacity) n_upper = sb.capacity;
   const uint32_t ntiles = (uint32_t)(((uint64_t)n_upper + RS_TILE - 1) / RS_TILE);
   int cur = 0;
   if (ntiles == 0) return cur;
   int passes, bpp;
-  sort_plan(end_bit - begin_bit, passes, bpp);
+  sort_plan(end_bit - begin_bit, passes, bpp, max_bits);
   const uint32_t grid = ntiles < (uint32_t)RS_GRID ? ntiles : (uint32_t)RS_GRID;
   for (int p = 0; p < passes; ++p) {
     const int shift = begin_bit + p * bpp;
@@ -357,7 +359,8 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
       case 4: launch_pass<4>(sb, cur, ident, d_n, shift, grid, st); break;
       case 5: launch_pass<5>(sb, cur, ident, d_n, shift, grid, st); break;
       case 6: launch_pass<6>(sb, cur, ident, d_n, shift, grid, st); break;
-      default: launch_pass<7>(sb, cur, ident, d_n, shift, grid, st); break;
+      case 7: launch_pass<7>(sb, cur, ident, d_n, shift, grid, st); break;
+      default: launch_pass<8>(sb, cur, ident, d_n, shift, grid < 148u ? grid : 148u, st); break;
     }
     cur ^= 1;
   }
