@@ -142,28 +142,46 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
         const uint32_t jj = c0 + lane;
         uint32_t rr = jj < m ? sRows[jj] : 1u;   // 1 = lo 1, hi 0: empty
         uint32_t mask = __ballot_sync(0xffffffffu, row >= (rr & 0xffu) && row <= (rr >> 8));
+        // two list entries per turn: their loads, quadratic forms and ex2 overlap; they are then
+        // applied to the pixel strictly in list order
         while (mask) {
-          const uint32_t k = c0 + __ffs(mask) - 1;
+          const uint32_t k0 = c0 + __ffs(mask) - 1;
           mask &= mask - 1;
-          const float4 a = sA[k];
-          const float4 b = sB[k];
-          const float2 c = sC[k];
-          const float dx = a.x - xf, dy = a.y - yf;
+          const bool two = mask != 0;
+          const uint32_t k1 = two ? c0 + __ffs(mask) - 1 : k0;
+          mask &= mask - 1;
+          const float4 a0 = sA[k0], a1 = sA[k1];
+          const float4 b0 = sB[k0], b1 = sB[k1];
+          const float2 e0 = sC[k0], e1 = sC[k1];
+          const float dx0 = a0.x - xf, dy0 = a0.y - yf, dx1 = a1.x - xf, dy1 = a1.y - yf;
           // power * log2e = dx*(hA*dx + nB*dy) + hC*dy*dy
-          const float power2 = fmaf(b.x * dy, dy, dx * fmaf(a.w, dy, a.z * dx));
-          if (power2 <= 0.f && power2 >= c.y && !done) {
-            const float alpha = fminf(0.99f, b.y * ex2_approx(power2));
-            if (alpha >= ALPHA_MIN) {
-              const float test_T = T * (1.f - alpha);
-              if (test_T < 0.0001f) {
-                done = true;
-                if (COUNT) stop_at = base + k + 1;
-              } else {
-                const float w = alpha * T;
-                Cr = fmaf(b.z, w, Cr); Cg = fmaf(b.w, w, Cg); Cb = fmaf(c.x, w, Cb); Ca = fmaf(b.y, w, Ca);
-                T = test_T;
-                if (COUNT) ++n_blend;
-              }
+          const float p0 = fmaf(b0.x * dy0, dy0, dx0 * fmaf(a0.w, dy0, a0.z * dx0));
+          const float p1 = fmaf(b1.x * dy1, dy1, dx1 * fmaf(a1.w, dy1, a1.z * dx1));
+          const bool v0 = p0 <= 0.f && p0 >= e0.y, v1 = two && p1 <= 0.f && p1 >= e1.y;
+          const float al0 = v0 ? fminf(0.99f, b0.y * ex2_approx(p0)) : 0.f;
+          const float al1 = v1 ? fminf(0.99f, b1.y * ex2_approx(p1)) : 0.f;
+          if (!done && al0 >= ALPHA_MIN) {
+            const float test_T = T * (1.f - al0);
+            if (test_T < 0.0001f) {
+              done = true;
+              if (COUNT) stop_at = base + k0 + 1;
+            } else {
+              const float w = al0 * T;
+              Cr = fmaf(b0.z, w, Cr); Cg = fmaf(b0.w, w, Cg); Cb = fmaf(e0.x, w, Cb); Ca = fmaf(b0.y, w, Ca);
+              T = test_T;
+              if (COUNT) ++n_blend;
+            }
+          }
+          if (!done && al1 >= ALPHA_MIN) {
+            const float test_T = T * (1.f - al1);
+            if (test_T < 0.0001f) {
+              done = true;
+              if (COUNT) stop_at = base + k1 + 1;
+            } else {
+              const float w = al1 * T;
+              Cr = fmaf(b1.z, w, Cr); Cg = fmaf(b1.w, w, Cg); Cb = fmaf(e1.x, w, Cb); Ca = fmaf(b1.y, w, Ca);
+              T = test_T;
+              if (COUNT) ++n_blend;
             }
           }
         }

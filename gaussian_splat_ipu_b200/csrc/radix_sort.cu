@@ -28,8 +28,10 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
 }
 
 __device__ __forceinline__ uint32_t num_elems(const uint32_t *d_n, uint32_t cap) {
+  // a count beyond the capacity means the producer overflowed the buffer and wrote an incomplete
+  // array (the host re-runs the frame): sort nothing rather than garbage
   const uint32_t n = *d_n;
-  return n < cap ? n : cap;
+  return n <= cap ? n : 0u;
 }
 
 constexpr int RS_WARPS = RS_THREADS / 32;
