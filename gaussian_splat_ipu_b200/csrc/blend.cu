@@ -241,9 +241,28 @@ tile_order_kernel(const uint2 *__restrict__ ranges, int tiles_across, int row_be
     atomicAdd(&cnt[order_bucket(len)], 1u);
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t run = 0;
-    for (int k = 0; k < ORDER_BUCKETS; ++k) { const uint32_t c = cnt[k]; cnt[k] = run; run += c; }
+  if (threadIdx.x < 32) {   // exclusive scan of the bucket counts: one warp, ORDER_BUCKETS / 32 (+1) per lane
+    constexpr int PER = (ORDER_BUCKETS + 31) / 32;
+    uint32_t v[PER], sum = 0;
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+      const int k = threadIdx.x * PER + q;
+      v[q] = k < ORDER_BUCKETS ? cnt[k] : 0u;
+      sum += v[q];
+    }
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (threadIdx.x >= o) inc += t;
+    }
+    uint32_t run = inc - sum;
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+      const int k = threadIdx.x * PER + q;
+      if (k < ORDER_BUCKETS) cnt[k] = run;
+      run += v[q];
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < ntiles; i += blockDim.x) {

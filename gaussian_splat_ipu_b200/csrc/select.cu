@@ -19,16 +19,18 @@
 namespace gsplat {
 
 // ---- thresholds: quantiles of a 4096-key sample, one CTA ----------------------------------------
-// fractions[s] (s < nthr) -> tau[s] = largest key value with (sample keys below it) <= fraction *
-// (drawn sample keys); found bit by bit (32 counting rounds over the register-resident sample).
+// fractions[s] -> tau[s] = the sample key of rank fraction * (drawn sample keys), found by a
+// four-round radix select over the register-resident sample.
 constexpr int QS_THREADS = 1024;
 constexpr int QS_PER_THREAD = 4;
 constexpr int QS_SAMPLE = QS_THREADS * QS_PER_THREAD;
 
 __global__ void __launch_bounds__(QS_THREADS)
 depth_quantile_kernel(const uint32_t *__restrict__ depth_key, uint32_t n, SliceFractions fr, uint32_t *__restrict__ tau) {
-  __shared__ uint32_t warp_cnt[QS_THREADS / 32];
-  __shared__ uint32_t total_s;
+  // radix select, 8 bits per round: histogram of the sample keys that share the prefix found so
+  // far, then the bin in which the running count crosses the target rank
+  __shared__ uint32_t hist[256];
+  __shared__ uint32_t sh_prefix, sh_rank, sh_drawn;
   const uint32_t tid = threadIdx.x;
   uint32_t key[QS_PER_THREAD];
 #pragma unroll
@@ -37,29 +39,52 @@ depth_quantile_kernel(const uint32_t *__restrict__ depth_key, uint32_t n, SliceF
     const uint64_t i = n > QS_SAMPLE ? (uint64_t)j * n / QS_SAMPLE : j;
     key[k] = i < n ? depth_key[i] : DEPTH_KEY_CULLED;
   }
-  auto count_below = [&](uint32_t bound) {   // sample keys < bound, over the CTA
+  {  // drawn sample keys
     uint32_t c = 0;
 #pragma unroll
-    for (int k = 0; k < QS_PER_THREAD; ++k) c += key[k] < bound ? 1u : 0u;
+    for (int k = 0; k < QS_PER_THREAD; ++k) c += key[k] != DEPTH_KEY_CULLED ? 1u : 0u;
+    if (tid == 0) sh_drawn = 0;
+    __syncthreads();
     c = __reduce_add_sync(0xffffffffu, c);
-    if ((tid & 31) == 0) warp_cnt[tid >> 5] = c;
+    if ((tid & 31) == 0 && c) atomicAdd(&sh_drawn, c);
     __syncthreads();
-    if (tid < 32) {
-      const uint32_t t = __reduce_add_sync(0xffffffffu, warp_cnt[tid]);
-      if (tid == 0) total_s = t;
-    }
-    __syncthreads();
-    return total_s;
-  };
-  const uint32_t drawn = count_below(DEPTH_KEY_CULLED);
+  }
+  const uint32_t drawn = sh_drawn;
   for (int s = 0; s < fr.count; ++s) {
-    const uint32_t target = (uint32_t)((double)drawn * fr.f[s]);
-    uint32_t t = 0;
-    for (int bit = 31; bit >= 0; --bit) {
-      const uint32_t cand = t | (1u << bit);
-      if (count_below(cand) <= target) t = cand;
+    // tau = the sample key of rank `target` among the drawn ones (0-based); keys below it form the slice
+    if (tid == 0) { sh_prefix = 0; sh_rank = min((uint32_t)((double)drawn * fr.f[s]), drawn ? drawn - 1 : 0u); }
+    for (int shift = 24; shift >= 0; shift -= 8) {
+      if (tid < 256) hist[tid] = 0;
+      __syncthreads();
+      const uint32_t prefix = sh_prefix, hi_mask = shift == 24 ? 0u : 0xffffffffu << (shift + 8);
+#pragma unroll
+      for (int k = 0; k < QS_PER_THREAD; ++k)
+        if (key[k] != DEPTH_KEY_CULLED && (key[k] & hi_mask) == prefix) atomicAdd(&hist[(key[k] >> shift) & 255u], 1u);
+      __syncthreads();
+      if (tid < 32) {   // one warp: find the bin where the running count passes the rank
+        uint32_t v[8], sum = 0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) { v[q] = hist[tid * 8 + q]; sum += v[q]; }
+        uint32_t inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+          if (tid >= o) inc += t;
+        }
+        const uint32_t rank = sh_rank;
+        uint32_t run = inc - sum;
+        if (rank >= run && rank < inc) {   // exactly one lane
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            if (rank >= run && rank < run + v[q]) { sh_prefix = prefix | ((tid * 8 + q) << shift); sh_rank = rank - run; }
+            run += v[q];
+          }
+        }
+      }
+      __syncthreads();
     }
-    if (tid == 0) tau[s] = t;
+    if (tid == 0) tau[s] = drawn ? sh_prefix : DEPTH_KEY_CULLED;
+    __syncthreads();
   }
 }
 
