@@ -239,7 +239,7 @@ def gpu_arm(args):
 
     g, base, proj, W, H = make_scene(args.workload)
     n = g.shape[0]
-    s = B200Splatter(g, W, H, device=local, collect_timings=True)
+    s = B200Splatter(g, W, H, device=local)     # production configuration: frame graphs, no stage events
     s.updateProjection(proj)
     s.updateFocalLengths(FOV, SCALE_DIV)
 
@@ -258,7 +258,6 @@ def gpu_arm(args):
     for k in range(Wm):
         step(k)
     s.sync()
-    s.timings_accum(reset=True)
 
     # ---- device-resident leg: scene in HBM, K frames back to back -----------------------------
     sampler = ClockSampler(local)
@@ -274,7 +273,6 @@ def gpu_arm(args):
     launches = launch_count() - l0
     barrier()
     clocks = sampler.finish()
-    tm, nframes = s.timings_accum(reset=True)
     st = s.stats()
     t_max = max_over_ranks(wall)
     dev_ms_max = max_over_ranks(dev_ms)
@@ -327,10 +325,24 @@ def gpu_arm(args):
         return
     # ---- accounting on rank 0 ------------------------------------------------------------------
     peaks, peak_src = measured_peaks()
-    step(Wm)
-    s.sync()
-    pairs, blended = s.count_pairs()
-    st = s.stats()
+    # per-stage device times: the same frames with cudaEvents between the stages (eager launches,
+    # not the captured frame), a bounded number of steps
+    s.close()
+    # same slicing as the production run settled on (its last frames), fixed so every timed frame is alike
+    sliced = st.depth_slices > 1 or st.num_duplicates < 0.6 * st.num_reference_duplicates
+    ss = B200Splatter(g, W, H, device=local, collect_timings=True, depth_slices=2 if sliced else 1)
+    ss.updateProjection(proj); ss.updateFocalLengths(FOV, SCALE_DIV)
+    for k in range(PREWARM_FRAMES):
+        ss.updateModelView(views[k % ORBIT_VIEWS]); ss.execute()
+    ss.sync()
+    ss.timings_accum(reset=True)
+    for k in range(min(K, 100)):
+        ss.updateModelView(views[((Wm + k) * world + rank) % ORBIT_VIEWS]); ss.execute()
+    tm, nframes = ss.timings_accum(reset=True)
+    ss.updateModelView(views[(Wm * world + rank) % ORBIT_VIEWS]); ss.execute(); ss.sync()
+    pairs, blended = ss.count_pairs()
+    st = ss.stats()
+    ss.close()
     stages = stage_rooflines(tm, st, pairs, blended, W, H, s.num_tiles, clocks["sm_mhz"], peaks)
     dom = max(stages, key=lambda k: stages[k]["ms"])
     r = stages[dom]
@@ -338,7 +350,6 @@ def gpu_arm(args):
                 "frac": r["frac"], "traffic": None, "peak_source": peak_src, "ms": r["ms"]}
     # the same frames with ONE depth slice (every tile's list complete, as the reference builds them):
     # reported beside the headline so the effect of the slices is visible; a bounded number of steps
-    s.close()
     s1 = B200Splatter(g, W, H, device=local, depth_slices=1)
     s1.updateProjection(proj); s1.updateFocalLengths(FOV, SCALE_DIV)
     K1 = min(K, 60)

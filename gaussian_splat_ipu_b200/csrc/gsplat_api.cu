@@ -57,6 +57,17 @@ enum Scalar { SC_V = 0, SC_OVERFLOW = 1, SC_TICKET0 = 8 /* K2 chain ticket per s
               SC_SELTICKET0 = 32 /* selection chain ticket per slice */, SC_TAU0 = 40 /* depth-key thresholds */,
               SC_FRAME_WORDS = 48, SC_N = 48, SC_SORT_N = 49, SC_COUNT = 64 };
 
+// A captured frame (CUDA graph): the whole stage sequence of one frame for one slicing mode.  Only
+// K1's camera argument changes from frame to frame; it is refreshed in place before each launch.
+struct FrameGraph {
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  cudaGraphNode_t k1 = nullptr;
+  cudaKernelNodeParams k1_params{};
+  int sorted_a = 0, sorted = 0;
+  unsigned long long launches = 0;
+};
+
 struct gsplat_ctx {
   gsplat_config cfg{};
   cudaStream_t st = nullptr;
@@ -99,6 +110,9 @@ struct gsplat_ctx {
   uint8_t *tile_state = nullptr;   // one block, zeroed per frame: TileState arrays
   TileState ts{};                  // per tile / per part: every pixel has stopped
   int blend_split = 1;             // K5 CTAs per semantic tile
+  // frame graphs: [0] one slice, [1] sliced; dropped whenever buffers, scene or band change
+  FrameGraph graphs[2];
+  bool use_graphs = true;          // GSPLAT_GRAPHS=0 disables (eager launches)
   float *tstate = nullptr;         // per pixel: transmittance carried between slices (-1 = stopped)
   unsigned long long *pair_counters = nullptr;   // non-null while a counting re-run is enqueued
   // parity tap: per-slice sorted lists of the last frame (filled only with cfg.debug_records)
@@ -142,12 +156,21 @@ int fail(gsplat_ctx *c, int code, const std::string &msg) {
 
 template <typename T> void dfree(T *&p) { if (p) { cudaFree(p); p = nullptr; } }
 
+void drop_graphs(gsplat_ctx *ctx) {
+  for (auto &g : ctx->graphs) {
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (g.graph) cudaGraphDestroy(g.graph);
+    g = FrameGraph{};
+  }
+}
+
 void free_sort(SortBuffers &s) {
   dfree(s.keys[0]); dfree(s.keys[1]); dfree(s.vals[0]); dfree(s.vals[1]); dfree(s.block_hist); dfree(s.digit_totals);
   s.capacity = 0; s.max_tiles = 0;
 }
 
 int alloc_sort(gsplat_ctx *ctx, SortBuffers &s, size_t capacity) {
+  drop_graphs(ctx);   // captured frames hold the old buffers' addresses
   if (capacity > 0xfffff000ull) return fail(ctx, GSPLAT_E_CAPACITY, "element count exceeds 32-bit indexing");
   cudaSetDevice(ctx->cfg.device);
   free_sort(s);
@@ -237,6 +260,7 @@ void gsplat_destroy(gsplat_ctx *ctx) {
                  (unsigned long long)ctx->mode_frames[0], ctx->ema_ms[0], (unsigned long long)ctx->mode_frames[1], ctx->ema_ms[1]);
   cudaSetDevice(ctx->cfg.device);
   if (ctx->st) cudaStreamSynchronize(ctx->st);
+  drop_graphs(ctx);
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
   dfree(ctx->proj.rec); dfree(ctx->proj.rect);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->d_scalars); dfree(ctx->lookback);
@@ -361,6 +385,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     if (const char *e = std::getenv("GSPLAT_K5_SPLIT")) split = std::atoi(e);
     if (split < 1 || split > BLEND_MAX_SPLIT || cfg->tile_h % split) split = 1;
     ctx->blend_split = split;
+    if (const char *e = std::getenv("GSPLAT_GRAPHS")) ctx->use_graphs = std::atoi(e) != 0;
     CUC(cudaMalloc(&ctx->tstate, sizeof(float) * px));
   }
 #undef CUC
@@ -373,6 +398,7 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   if (n > 0x7fffffffull) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: too many Gaussians");
   CU(cudaSetDevice(ctx->cfg.device));
   CU(cudaStreamSynchronize(ctx->st));
+  drop_graphs(ctx);
   for (auto &sl : ctx->slots) sl.pending = false;
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
   dfree(ctx->proj.rec); dfree(ctx->proj.rect); dfree(ctx->lookback);
@@ -451,6 +477,11 @@ int gsplat_set_band(gsplat_ctx *ctx, int row_begin, int row_end) {
   if (!ctx) return GSPLAT_E_ARG;
   if (row_begin < 0 || row_end > ctx->tiles_down || row_begin > row_end)
     return fail(ctx, GSPLAT_E_ARG, "gsplat_set_band: bad tile-row band");
+  if (row_begin != ctx->cfg.band_row_begin || row_end != ctx->cfg.band_row_end) {
+    cudaSetDevice(ctx->cfg.device);
+    cudaStreamSynchronize(ctx->st);   // captured frames of the old band may still be running
+    drop_graphs(ctx);
+  }
   ctx->cfg.band_row_begin = row_begin;
   ctx->cfg.band_row_end = row_end;
   ctx->fp.row_begin = row_begin;

@@ -245,6 +245,8 @@ void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st) {
   aos_to_soa_kernel<<<ceil_div(scene.n, 256), 256, 0, st>>>(reinterpret_cast<const float4 *>(aos16), scene);
 }
 
+const void *project_kernel_address() { return reinterpret_cast<const void *>(&project_kernel); }
+
 void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *drawn_counter,
                     float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st) {
   if (!scene.n) return;
