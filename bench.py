@@ -298,7 +298,7 @@ def gpu_arm(args):
     sync_fps = world * K / sync_wall
     checksum_sync = int(frame.array[::7, ::7].astype(np.uint64).sum()) + int(counts.sum())
 
-    # (b) the two-deep frame stream (imagePtr/imagePtrBuffered swap, src/main/splat.cpp:281-283):
+    # (b) the frame stream (imagePtr/imagePtrBuffered swap, src/main/splat.cpp:281-283):
     #     every step uploads its camera, enqueues its frame and takes delivery of the previous
     #     frame in pinned host memory; the last frame is delivered inside the timed region too
     for k in range(2):
@@ -306,14 +306,15 @@ def gpu_arm(args):
     barrier()
     checksum = 0
     t0 = time.perf_counter()
-    set_view(Wm); prev = s.executeStreamed()
-    for k in range(1, K):
+    inflight = []                      # up to two frames rendering / crossing PCIe behind the one delivered
+    for k in range(K):
         set_view(Wm + k)
-        nxt = s.executeStreamed()
-        img, counts = s.acquireFrame(prev)
-        checksum += int(img[540 % H, ::64, 1].sum()) + int(counts[0])    # touch the delivered frame
-        prev = nxt
-    img, counts = s.acquireFrame(prev)
+        inflight.append(s.executeStreamed())
+        if len(inflight) > 2:
+            img, counts = s.acquireFrame(inflight.pop(0))
+            checksum += int(img[540 % H, ::64, 1].sum()) + int(counts[0])    # touch the delivered frame
+    while inflight:
+        img, counts = s.acquireFrame(inflight.pop(0))
     e2e_wall = max_over_ranks(time.perf_counter() - t0)
     barrier()
     e2e_fps = world * K / e2e_wall
@@ -387,7 +388,7 @@ def gpu_arm(args):
                       "max_tile_count": int(st.max_tile_count), "pairs": pairs, "blended": blended},
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": 34 * 4,
                     "d2h_bytes_per_step": W * H * 3 + s.num_tiles * 4 + 12,
-                    "api": "executeStreamed/acquireFrame: two-deep frame stream, every frame delivered to pinned "
+                    "api": "executeStreamed/acquireFrame: three-slot frame stream, every frame delivered to pinned "
                            "host memory inside the timed region",
                     "checksum": checksum_last, "same_frame_as_sequential": checksum_last == checksum_sync,
                     "sequential": {"value": sync_fps, "unit": "frames/s",

@@ -192,7 +192,7 @@ int ceil_log2(uint32_t v) { int b = 0; while ((1u << b) < v) ++b; return b; }
 
 // Depth slices: cumulative fractions of the drawn Gaussians (nearest first) at which the frame is
 // cut.  The first slice is small (dense tiles saturate within their first few thousand Gaussians:
-// 1/16 with the default two slices), further cuts are spaced geometrically up to 1.
+// 8 % with the default two slices), further cuts are spaced geometrically up to 1.
 // depth_slices == 1: one slice (every tile's list complete, the reference's lists).  Scenes too
 // small to be worth cutting get one slice.  GSPLAT_SLICE_FRACTIONS="f0,f1,..." overrides
 // (experiments; the last slice always ends at 1).
@@ -201,7 +201,7 @@ void plan_slices(gsplat_ctx *ctx) {
   int want = ctx->cfg.depth_slices ? ctx->cfg.depth_slices : GSPLAT_DEFAULT_DEPTH_SLICES;
   if (!ctx->cfg.depth_slices && n < 65536) want = 1;
   double frac[MAX_SLICES];
-  for (int s = 0; s < want; ++s) frac[s] = std::pow(0.0625, (double)(want - 1 - s) / (want > 2 ? 0.5 * (want - 1) : 1.0));
+  for (int s = 0; s < want; ++s) frac[s] = std::pow(0.08, (double)(want - 1 - s) / (want > 2 ? 0.5 * (want - 1) : 1.0));
   if (const char *e = std::getenv("GSPLAT_SLICE_FRACTIONS")) {
     if (!ctx->cfg.depth_slices) {
       int k = 0;

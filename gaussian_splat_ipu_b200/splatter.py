@@ -238,7 +238,7 @@ class B200Splatter:
 
     def acquireFrame(self, ticket: int):
         """Waits for a streamed frame; returns ((H, W, 3) BGR8, (num_tiles,) counts) as views of the
-        context's pinned slot, valid until the second-next executeStreamed()."""
+        context's pinned slot, valid until the third-next executeStreamed()."""
         b, c = _vp(), _vp()
         self._check(self.lib.gsplat_acquire_frame(self.h, ticket, C.byref(b), C.byref(c)))
         img = np.frombuffer((C.c_uint8 * (self.height * self.width * 3)).from_address(b.value), np.uint8)

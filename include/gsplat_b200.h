@@ -120,7 +120,7 @@ int gsplat_read_tile_counts(gsplat_ctx *ctx, uint32_t *dst);
 /* ---- double-buffered frame stream ---------------------------------------------------------------
  * The render loop of the reference renders into one cv::Mat while its AsyncTask thread encodes /
  * sends the previous one, then swaps them (src/main/splat.cpp:215-226,281-283: imagePtr /
- * imagePtrBuffered).  The same two-deep pipeline, with the device-to-host copy inside it:
+ * imagePtrBuffered).  The same pipeline, GSPLAT_STREAM_SLOTS deep, with the device-to-host copy inside it:
  *
  *   gsplat_render_streamed   gsplat_render() + the BGR8 post-process, then an asynchronous copy of
  *                            the BGR8 image and the per-tile counts into one of the context's
@@ -130,11 +130,11 @@ int gsplat_read_tile_counts(gsplat_ctx *ctx, uint32_t *dst);
  *   gsplat_acquire_frame     waits for that ticket's copy and hands out pointers INTO the pinned
  *                            slot: *bgr8 = height rows of 3*width bytes (getFrameBuffer's image),
  *                            *counts = tiles_across*tiles_down values (getIPUHistogram).  Either may
- *                            be NULL.  The pointers stay valid until the second-next
+ *                            be NULL.  The pointers stay valid until the third-next
  *                            gsplat_render_streamed (the slot is then re-used); a ticket older than
  *                            that fails with GSPLAT_E_STATE.  A frame that overflowed the duplicate
  *                            buffer is re-run here (same camera) before the call returns.          */
-#define GSPLAT_STREAM_SLOTS 2
+#define GSPLAT_STREAM_SLOTS 3
 int gsplat_render_streamed(gsplat_ctx *ctx, uint64_t *ticket);
 int gsplat_acquire_frame(gsplat_ctx *ctx, uint64_t ticket, const uint8_t **bgr8, const uint32_t **counts);
 

@@ -99,10 +99,10 @@ public:
     check(gsplat_read_tile_counts(ctx_, counts.data()));
   }
 
-  // Two-deep frame stream: the render loop's imagePtr / imagePtrBuffered swap
+  // Frame stream (three slots): the render loop's imagePtr / imagePtrBuffered swap
   // (src/main/splat.cpp:215-226,281-283) with the device-to-host copy inside the pipeline.
   // executeStreamed() returns a ticket at once; acquireFrame(ticket, ...) waits for that frame and
-  // points into pinned host memory that stays valid until the second-next executeStreamed().
+  // points into pinned host memory that stays valid until the third-next executeStreamed().
   std::uint64_t executeStreamed() {
     check(gsplat_set_camera(ctx_, modelView_, projection_, fov_, scaleDiv_));
     std::uint64_t t = 0;
