@@ -40,7 +40,8 @@ __device__ __forceinline__ float ex2_approx(float x) {
 //   sA float4: mean.x, mean.y, -0.5*log2e*A, -log2e*B     sB float4: -0.5*log2e*C, opacity, r, g
 //   sC float2: b, conservative log2 threshold (skip when power2 < it)
 //   sRows u16: row_lo | row_hi << 8 ; lo > hi: touches no row
-constexpr size_t BLEND_SMEM_PER_THREAD = 16 + 16 + 8 + 2;
+constexpr uint32_t BLEND_BATCH = 2;   // list entries staged per thread and batch
+constexpr size_t BLEND_SMEM_PER_THREAD = BLEND_BATCH * (16 + 16 + 8 + 2);
 
 //
 // Depth slices (see duplicate.cu): the list of a tile may arrive in several consecutive pieces, one
@@ -59,9 +60,9 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   const uint32_t tid = threadIdx.x, lane = tid & 31, row = tid >> 5;
   const uint32_t nthreads = blockDim.x;
   float4 *sA = reinterpret_cast<float4 *>(blend_smem_raw);
-  float4 *sB = sA + nthreads;
-  float2 *sC = reinterpret_cast<float2 *>(sB + nthreads);
-  uint16_t *sRows = reinterpret_cast<uint16_t *>(sC + nthreads);
+  float4 *sB = sA + BLEND_BATCH * nthreads;
+  float2 *sC = reinterpret_cast<float2 *>(sB + BLEND_BATCH * nthreads);
+  uint16_t *sRows = reinterpret_cast<uint16_t *>(sC + BLEND_BATCH * nthreads);
   // a CTA blends `tile_h` consecutive rows of a semantic tile (a "part": the whole tile, or 1/nsub
   // of it so that a crowded tile's list is walked by several SMs at once); parts of one tile are
   // neighbours in the grid
@@ -91,9 +92,12 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   uint32_t stop_at = done ? 0u : n;   // COUNT: list entries this pixel visits (reference semantics)
   unsigned long long n_blend = 0;  // COUNT
 
-  for (uint32_t base = 0; base < n; base += nthreads) {
+  const uint32_t batch = BLEND_BATCH * nthreads;   // list entries staged per barrier pair
+  for (uint32_t base = 0; base < n; base += batch) {
     // ---- stage one batch: gather the record, prescale, derive the row range ----------------
-    const uint32_t j = base + tid;
+#pragma unroll
+    for (uint32_t sb = 0; sb < BLEND_BATCH; ++sb) {
+    const uint32_t slot = sb * nthreads + tid, j = base + slot;
     if (j < n) {
       const uint32_t g = vals[range.x + j];
       const float4 *r = p.rec + (size_t)g * 3;   // 48 contiguous bytes: two sectors of one line
@@ -130,13 +134,14 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
           if (lo > hi) { lo = 1; hi = 0; }
         }
       }
-      sA[tid] = make_float4(a.x, a.y, -0.5f * LOG2E * A, -LOG2E * B);
-      sB[tid] = make_float4(-0.5f * LOG2E * C, op, b.z, b.w);
-      sC[tid] = make_float2(cb, thr2);
-      sRows[tid] = (uint16_t)(lo | (hi << 8));
+      sA[slot] = make_float4(a.x, a.y, -0.5f * LOG2E * A, -LOG2E * B);
+      sB[slot] = make_float4(-0.5f * LOG2E * C, op, b.z, b.w);
+      sC[slot] = make_float2(cb, thr2);
+      sRows[slot] = (uint16_t)(lo | (hi << 8));
+    }
     }
     __syncthreads();
-    const uint32_t m = min(nthreads, n - base);
+    const uint32_t m = min(batch, n - base);
     if (!__all_sync(0xffffffffu, done)) {
       for (uint32_t c0 = 0; c0 < m; c0 += 32) {
         const uint32_t jj = c0 + lane;

@@ -71,7 +71,7 @@ struct SortBuffers {
   uint32_t max_tiles;
 };
 constexpr int RS_THREADS = 256;
-constexpr int RS_ITEMS = 16;
+constexpr int RS_ITEMS = 8;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
 constexpr int RS_MAX_BITS = 7;      // digit width limit of the counter-based ranking (128 digits)
 constexpr int RS_GRID = 148 * 3;   // CTAs walk RS_TILE-element tiles with a grid stride

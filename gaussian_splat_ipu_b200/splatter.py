@@ -180,6 +180,7 @@ class B200Splatter:
         self._mv = np.eye(4, dtype=np.float32)
         self._proj = np.eye(4, dtype=np.float32)
         self._fxy = (float(np.radians(np.float32(40.0))), 0.1)
+        self._slot_views = {}
         g = np.ascontiguousarray(gaussians16, dtype=np.float32).reshape(-1, 16)
         self.n = g.shape[0]
         self._check(self.lib.gsplat_upload_scene(self.h, g.ctypes.data_as(_fp), self.n))
@@ -241,9 +242,12 @@ class B200Splatter:
         context's pinned slot, valid until the third-next executeStreamed()."""
         b, c = _vp(), _vp()
         self._check(self.lib.gsplat_acquire_frame(self.h, ticket, C.byref(b), C.byref(c)))
-        img = np.frombuffer((C.c_uint8 * (self.height * self.width * 3)).from_address(b.value), np.uint8)
-        cnt = np.frombuffer((C.c_uint32 * self.num_tiles).from_address(c.value), np.uint32)
-        return img.reshape(self.height, self.width, 3), cnt
+        views = self._slot_views.get(b.value)      # the slots are few and fixed: wrap each once
+        if views is None:
+            img = np.frombuffer((C.c_uint8 * (self.height * self.width * 3)).from_address(b.value), np.uint8)
+            cnt = np.frombuffer((C.c_uint32 * self.num_tiles).from_address(c.value), np.uint32)
+            views = self._slot_views[b.value] = (img.reshape(self.height, self.width, 3), cnt)
+        return views
 
     def getFrameBuffer(self, out: np.ndarray | None = None) -> np.ndarray:
         """(H, W, 3) BGR8 image, ipu_rasteriser.cpp:131-144."""
