@@ -131,3 +131,26 @@ def test_cpp_shim_compiles_and_fails_loudly_without_device(tmp_path):
     exe = _build_shim_smoke(str(tmp_path))
     r = subprocess.run([exe, "1000"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 3 and "no CPU fallback" in r.stdout, (r.returncode, r.stdout, r.stderr)
+
+
+def test_cpp_host_driver_builds_and_fails_loudly_without_a_device():
+    """apps/splat_b200 links against the C ABI; with no CUDA device it reports the library's error
+    (exit code 3) instead of rendering on the CPU."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sp.build_library()
+    subprocess.run(["make", "-C", os.path.join(root, "apps")], check=True, capture_output=True)
+    r = subprocess.run([os.path.join(root, "apps", "splat_b200"), "--synthetic", "1000", "--frames", "2"],
+                       capture_output=True, text=True, timeout=60)
+    import ctypes
+    try:
+        ctypes.CDLL("libcuda.so.1")
+        have_driver = True
+    except OSError:
+        have_driver = False
+    if r.returncode == 0:
+        assert r.stdout.startswith("ok ")          # a GPU box
+    else:
+        assert r.returncode == 3 and r.stdout.startswith("no-device:"), r.stdout + r.stderr
+    assert subprocess.run([os.path.join(root, "apps", "splat_b200")], capture_output=True).returncode == 2   # usage
