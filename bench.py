@@ -127,6 +127,22 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
 
 
+def frame_traffic():
+    """Per-stage DRAM bytes of one frame from the newest committed ncu capture
+    (profiles/traffic_r*.json, written by profiles/traffic_frame.py); {} if there is none."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "traffic_r*.json")), key=os.path.getmtime)
+    for f in reversed(files):
+        try:
+            with open(f) as fh:
+                d = json.load(fh)
+            if "stages" in d:
+                return {k: v["dram_bytes"] for k, v in d["stages"].items()}, os.path.basename(f)
+        except Exception:
+            pass
+    return {}, None
+
+
 def host_threads():
     """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1: ignore it, the CPU
     arm is meant to use the whole host)."""
@@ -347,8 +363,10 @@ def gpu_arm(args):
     stages = stage_rooflines(tm, st, pairs, blended, W, H, s.num_tiles, clocks["sm_mhz"], peaks)
     dom = max(stages, key=lambda k: stages[k]["ms"])
     r = stages[dom]
+    traffic, traffic_src = frame_traffic()
     roofline = {"kernel": dom, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
-                "frac": r["frac"], "traffic": None, "peak_source": peak_src, "ms": r["ms"]}
+                "frac": r["frac"], "traffic": traffic.get(dom), "traffic_unit": "DRAM bytes per frame, all launches of the stage",
+                "traffic_source": traffic_src, "algorithmic_bytes": r.get("alg_bytes"), "peak_source": peak_src, "ms": r["ms"]}
     # the same frames with ONE depth slice (every tile's list complete, as the reference builds them):
     # reported beside the headline so the effect of the slices is visible; a bounded number of steps
     s1 = B200Splatter(g, W, H, device=local, depth_slices=1)
