@@ -225,3 +225,25 @@ def ui_view(model_view, env_deg=0.0, env_deg2=0.0, X=640.0, Y=360.0, Z=1.0) -> n
 
 
 DEFAULT_FOV = float(np.radians(F32(40.0)))   # src/main/splat.cpp:170,175
+
+
+def multiview_cameras(g16: np.ndarray, n_orbit: int = 32, n_spiral: int = 32) -> list[np.ndarray]:
+    """The multi-view batch of BASELINE configs[4] / SURVEY §8(d) config 5: `n_orbit` cameras on
+    the app's orbit at 1.0x the bounding-box radius (``lookAtBoundingBox(bb,(0,1,1),1)`` rotated
+    about y in equal steps, as ``src/main/splat.cpp:245-262`` turns the model), then `n_spiral`
+    cameras on a two-turn spiral from 0.6x down to 0.05x the radius INSIDE the cloud, each looking
+    at the centroid.  In-cloud views are the load-imbalance stress: Gaussians next to the eye
+    cover many tiles and a few tiles hold most of the frame's list entries."""
+    bb = bounds(g16[:, 0:3])
+    bmin, bmax = bb
+    centre = (bmax + bmin) * F32(0.5)
+    radius = np.sqrt(np.dot(bmax - bmin, bmax - bmin), dtype=F32) * F32(0.5)
+    base = look_at_bounding_box(bb, (0.0, 1.0, 1.0), 1.0)
+    views = [rotate(base, np.radians(F32(360.0 / n_orbit * k)), (0.0, 1.0, 0.0)) for k in range(n_orbit)]
+    for k in range(n_spiral):
+        t = F32(k) / F32(max(n_spiral - 1, 1))
+        r = radius * (F32(0.6) + (F32(0.05) - F32(0.6)) * t)
+        ang = F32(4.0 * np.pi) * t
+        eye = centre + r * np.array([np.cos(ang), F32(0.35) * np.sin(F32(0.5) * ang), np.sin(ang)], dtype=F32)
+        views.append(look_at(eye.astype(F32), centre, (0.0, 1.0, 0.0)))
+    return views
