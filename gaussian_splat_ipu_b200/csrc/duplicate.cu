@@ -46,20 +46,6 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *warp_t
   return r;
 }
 
-// look-back word: flag in the top two bits, 62-bit value below (one 64-bit store publishes both)
-constexpr unsigned long long LB_AGGREGATE = 1ull << 62;   // value = this CTA's own total
-constexpr unsigned long long LB_PREFIX = 2ull << 62;      // value = inclusive prefix up to this CTA
-constexpr unsigned long long LB_VALUE = (1ull << 62) - 1;
-
-__device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long long *p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_relaxed(unsigned long long *p, unsigned long long v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
 // One CTA = one link of the chain = K2_CHUNK consecutive positions of the depth order
 // (K2_ITEMS per thread, striped so the loads coalesce and the rectangle gathers overlap).
 //
@@ -166,29 +152,7 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_gauss, const u
 
   // ---- chained scan: publish the aggregate, look back for the exclusive prefix ------------------
   if (tid < 32) {
-    unsigned long long excl = 0;
-    if (b == 0) {
-      if (tid == 0) st_relaxed(&lookback[0], LB_PREFIX | total);
-    } else {
-      if (tid == 0) st_relaxed(&lookback[b], LB_AGGREGATE | total);
-      int pos = (int)b - 1;
-      while (true) {   // one warp inspects 32 predecessors at a time
-        const int q = pos - (int)tid;
-        unsigned long long w = LB_PREFIX;   // positions before the chain start count as prefix 0
-        if (q >= 0) {
-          do { w = ld_relaxed(&lookback[q]); } while ((w >> 62) == 0);
-        }
-        const uint32_t is_prefix = __ballot_sync(0xffffffffu, (w >> 62) == 2);
-        const int first = is_prefix ? __ffs(is_prefix) - 1 : 32;   // nearest predecessor with a full prefix
-        unsigned long long v = (int)tid <= first ? (w & LB_VALUE) : 0;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        excl += v;
-        if (is_prefix) break;
-        pos -= 32;
-      }
-      if (tid == 0) st_relaxed(&lookback[b], LB_PREFIX | (excl + total));
-    }
+    const unsigned long long excl = lb_exclusive_prefix(lookback, b, total, tid);
     if (tid == 0) {
       const unsigned long long incl = excl + total;
       if (b == nblk - 1) *total_out = incl > 0xffffffffull ? 0xffffffffu : (uint32_t)incl;

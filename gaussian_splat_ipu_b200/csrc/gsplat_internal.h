@@ -44,6 +44,72 @@ struct Projected {
   uint2 *rect;           // {c0 | c1<<16, r0 | r1<<16} again, compact (8 B): K2 gathers it in depth
                          // order, and a random 8 B read costs one 32 B sector instead of a 48 B record
 };
+// ---- chained scan with decoupled look-back (K2 and the slice selection) ------------------------
+// One 64-bit word per chain link: flag in the top two bits, value below, so one store publishes both.
+constexpr unsigned long long LB_AGGREGATE = 1ull << 62;   // value = this link's own total
+constexpr unsigned long long LB_PREFIX = 2ull << 62;      // value = inclusive prefix up to this link
+constexpr unsigned long long LB_VALUE = (1ull << 62) - 1;
+#ifndef GSPLAT_LB_WINDOW
+#define GSPLAT_LB_WINDOW 1
+#endif
+constexpr int LB_WINDOW = GSPLAT_LB_WINDOW;   // predecessors inspected per lane and round (32 * LB_WINDOW links);
+                                              // measured (profiles/micro/chain.cu): 128-link rounds are slower than 32
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned long long lb_load(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void lb_store(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// Called by ONE full warp of link `b` after it knows its own `total`: publishes it, walks back over
+// the predecessors until one with a full prefix is found, publishes this link's inclusive prefix
+// and returns the exclusive one (all lanes).  Every predecessor is already running (links take
+// their position from an atomic ticket), so the spin on an unpublished word terminates.
+__device__ __forceinline__ unsigned long long lb_exclusive_prefix(unsigned long long *lookback, uint32_t b,
+                                                                  unsigned long long total, uint32_t lane) {
+  unsigned long long excl = 0;
+  if (b == 0) {
+    if (lane == 0) lb_store(&lookback[0], LB_PREFIX | total);
+    return 0;
+  }
+  if (lane == 0) lb_store(&lookback[b], LB_AGGREGATE | total);
+  int pos = (int)b - 1;
+  while (true) {
+    unsigned long long w[LB_WINDOW];
+#pragma unroll
+    for (int j = 0; j < LB_WINDOW; ++j) {   // distance from b-1: lane + 32 j; issue all loads, then wait
+      const int q = pos - (int)lane - 32 * j;
+      w[j] = q >= 0 ? lb_load(&lookback[q]) : LB_PREFIX;   // before the chain start: prefix 0
+    }
+#pragma unroll
+    for (int j = 0; j < LB_WINDOW; ++j) {
+      const int q = pos - (int)lane - 32 * j;
+      while ((w[j] >> 62) == 0) w[j] = lb_load(&lookback[q]);
+    }
+    bool found = false;
+    unsigned long long v = 0;
+#pragma unroll
+    for (int j = 0; j < LB_WINDOW; ++j) {
+      const uint32_t is_prefix = __ballot_sync(0xffffffffu, (w[j] >> 62) == 2);
+      if (!found) {
+        const int first = is_prefix ? __ffs(is_prefix) - 1 : 32;   // nearest link of this row with a full prefix
+        if ((int)lane <= first) v += w[j] & LB_VALUE;
+        found = is_prefix != 0;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    excl += v;
+    if (found) break;
+    pos -= 32 * LB_WINDOW;
+  }
+  if (lane == 0) lb_store(&lookback[b], LB_PREFIX | (excl + total));
+  return excl;
+}
+#endif
+
 constexpr uint32_t DEPTH_KEY_CULLED = 0xffffffffu;
 constexpr uint32_t RECT_EMPTY = 1u;   // {lo = 1, hi = 0}: the rectangle of a Gaussian that is not drawn
 

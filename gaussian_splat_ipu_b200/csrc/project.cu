@@ -51,7 +51,7 @@ __constant__ unsigned long long EXPF_TAB[32] = {
     0x3feee89f995ad3adull, 0x3feeff76f2fb5e47ull, 0x3fef199bdd85529cull, 0x3fef3720dcef9069ull,
     0x3fef5818dcfba487ull, 0x3fef7c97337b9b5full, 0x3fefa4afa2a490daull, 0x3fefd0765b6e4540ull,
 };
-__device__ __forceinline__ float exp_ref(float x) {
+__device__ __forceinline__ float exp_ref(float x, const unsigned long long *tab /* EXPF_TAB in shared memory */) {
   if (!(x == x)) return x + x;
   if (x > 88.72283172607421875f) return __int_as_float(0x7f800000);    // 0x1.62e42ep6f: overflow
   if (x < -103.97207641601562500f) return 0.0f;                        // -0x1.9fe368p6f: underflow
@@ -63,7 +63,7 @@ __device__ __forceinline__ float exp_ref(float x) {
   const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
   kd -= SHIFT;
   const double r = z - kd;
-  const double s = __longlong_as_double((long long)(EXPF_TAB[ki & 31ull] + (ki << 47)));
+  const double s = __longlong_as_double((long long)(tab[ki & 31ull] + (ki << 47)));
   const double zz = C0 * r + C1, r2 = r * r;
   double y = C2 * r + 1.0;
   y = zz * r2 + y;
@@ -102,6 +102,11 @@ __global__ void __launch_bounds__(K1_THREADS)
 project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__ drawn_counter,
                float *__restrict__ dbg_rec8, int32_t *__restrict__ dbg_rect4) {
   __shared__ uint32_t red[K1_THREADS / 32];
+  // the exp table is indexed per thread: from constant memory every distinct index of a warp is a
+  // separate replay, from shared memory it is one (at worst two-way conflicted) access
+  __shared__ unsigned long long exp_tab[32];
+  if (threadIdx.x < 32) exp_tab[threadIdx.x] = EXPF_TAB[threadIdx.x];
+  __syncthreads();
   const uint32_t i = blockIdx.x * K1_THREADS + threadIdx.x;
   uint32_t touched = 0;
   if (i < s.n) {
@@ -146,7 +151,7 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
       for (int c = 0; c < 3; ++c)
 #pragma unroll
         for (int k = 0; k < 3; ++k) S.c[c][k] = 0.f;
-      S.c[0][0] = exp_ref(sc0); S.c[1][1] = exp_ref(sc1); S.c[2][2] = exp_ref(sc2);
+      S.c[0][0] = exp_ref(sc0, exp_tab); S.c[1][1] = exp_ref(sc1, exp_tab); S.c[2][2] = exp_ref(sc2, exp_tab);
       const M3 cov3 = m3_mul(m3_mul(m3_mul(R, S), m3_t(S)), m3_t(R));
 
       // ---- Gaussian3D::ComputeCov2D, ipu_geometry.hpp:333-383.  mv is the FULL projection*view

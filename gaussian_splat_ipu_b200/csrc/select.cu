@@ -102,16 +102,6 @@ void launch_depth_quantiles(const uint32_t *depth_key, uint32_t n, const SliceFr
 constexpr int SEL_THREADS = 256;
 constexpr int SEL_ITEMS = 16;
 constexpr int SEL_CHUNK = SEL_THREADS * SEL_ITEMS;
-constexpr unsigned long long SLB_AGG = 1ull << 62, SLB_PREFIX = 2ull << 62, SLB_VALUE = (1ull << 62) - 1;
-
-__device__ __forceinline__ unsigned long long sel_ld(const unsigned long long *p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void sel_st(unsigned long long *p, unsigned long long v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
 
 template <bool CHECK_DONE>
 __global__ void __launch_bounds__(SEL_THREADS)
@@ -171,29 +161,7 @@ select_kernel(const uint32_t *__restrict__ depth_key, const uint2 *__restrict__ 
   const uint32_t total = wc[NWC];
   // chained scan over CTAs (same scheme as K2's)
   if (warp == 0) {
-    unsigned long long excl = 0;
-    if (b == 0) {
-      if (lane == 0) sel_st(&lookback[0], SLB_PREFIX | total);
-    } else {
-      if (lane == 0) sel_st(&lookback[b], SLB_AGG | total);
-      int pos = (int)b - 1;
-      while (true) {
-        const int q = pos - (int)lane;
-        unsigned long long w = SLB_PREFIX;
-        if (q >= 0) {
-          do { w = sel_ld(&lookback[q]); } while ((w >> 62) == 0);
-        }
-        const uint32_t is_prefix = __ballot_sync(0xffffffffu, (w >> 62) == 2);
-        const int firstp = is_prefix ? __ffs(is_prefix) - 1 : 32;
-        unsigned long long v = (int)lane <= firstp ? (w & SLB_VALUE) : 0;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        excl += v;
-        if (is_prefix) break;
-        pos -= 32;
-      }
-      if (lane == 0) sel_st(&lookback[b], SLB_PREFIX | (excl + total));
-    }
+    const unsigned long long excl = lb_exclusive_prefix(lookback, b, total, lane);
     if (lane == 0) {
       chain_s = (uint32_t)excl;
       if (b == gridDim.x - 1) *total_out = (uint32_t)(excl + total);
