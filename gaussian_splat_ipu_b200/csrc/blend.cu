@@ -11,15 +11,16 @@
 // There is no per-pixel bbox test in the reference: a Gaussian contributes to exactly the pixels
 // of the 32x20 tiles its rectangle covers, so the CTA *is* the semantic tile.
 //
-// Mapping: one CTA per tile, one warp per pixel ROW of the tile (32 px), one pixel per thread in
-// registers.  The list is staged through shared memory in batches of blockDim.x records gathered
-// by index; the staging thread also derives, per Gaussian, the rows of the tile on which
-// alpha >= 1/255 is possible at all (y-extent of the ellipse power >= ln(1/(255 opacity)),
-// conservative).  Each row-warp ballots over those row ranges and only walks the Gaussians that
-// can touch its row: skipped pairs are exactly pairs the reference loop `continue`s over, so the
-// result is unchanged while tiny splats cost ~nothing on the rows they miss.
+// Mapping: one CTA per tile (or column strip of it), one warp per 8 x 4 pixel BLOCK, one pixel per
+// thread in registers.  The list is staged through shared memory in batches of records gathered
+// by index; the staging thread also derives, per Gaussian, the rows and 8-pixel column blocks of
+// the part on which alpha >= 1/255 is possible at all (extent of the ellipse
+// power >= ln(1/(255 opacity)), conservative).  Each warp ballots over those extents and only
+// walks the Gaussians that can touch its block: skipped pairs are exactly pairs the reference loop
+// `continue`s over, so the result is unchanged while small splats cost ~nothing on the blocks
+// they miss.
 // exp() is ex2.approx.ftz on a log2e-prescaled conic.  FP32-pipe bound; no tensor cores (each
-// pair has its own quadratic form).  Stores are 512 B contiguous per warp.
+// pair has its own quadratic form).  Stores are four 128 B row segments per warp.
 #include "gsplat_internal.h"
 
 namespace gsplat {
@@ -39,7 +40,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
 // Shared-memory batch, blockDim.x entries of each (dynamic, sized by the launcher):
 //   sA float4: mean.x, mean.y, -0.5*log2e*A, -log2e*B     sB float4: -0.5*log2e*C, opacity, r, g
 //   sC float2: b, conservative log2 threshold (skip when power2 < it)
-//   sRows u16: row_lo | row_hi << 8 ; lo > hi: touches no row
+//   sRows u16: row_lo | row_hi << 5 | mask of the part's 8-pixel column blocks << 10 ; 1: touches nothing
 constexpr uint32_t BLEND_BATCH = 2;   // list entries staged per thread and batch
 constexpr size_t BLEND_SMEM_PER_THREAD = BLEND_BATCH * (16 + 16 + 8 + 2);
 
@@ -52,7 +53,7 @@ constexpr size_t BLEND_SMEM_PER_THREAD = BLEND_BATCH * (16 + 16 + 8 + 2);
 template <bool COUNT, bool FIRST, bool LAST>
 __global__ void __launch_bounds__(BLEND_MAX_ROWS * 32)
 blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
-             int tiles_across, int row_begin, int full_tile_h, int tile_h, float4 *__restrict__ fb,
+             int tiles_across, int row_begin, int full_tile_h, int part_w, float4 *__restrict__ fb,
              float *__restrict__ tstate, TileState ts, const uint32_t *__restrict__ order,
              unsigned long long *__restrict__ pair_counters) {
   extern __shared__ __align__(16) unsigned char blend_smem_raw[];
@@ -63,27 +64,35 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   float4 *sB = sA + BLEND_BATCH * nthreads;
   float2 *sC = reinterpret_cast<float2 *>(sB + BLEND_BATCH * nthreads);
   uint16_t *sRows = reinterpret_cast<uint16_t *>(sC + BLEND_BATCH * nthreads);
-  // a CTA blends `tile_h` consecutive rows of a semantic tile (a "part": the whole tile, or 1/nsub
-  // of it so that a crowded tile's list is walked by several SMs at once); parts of one tile are
-  // neighbours in the grid
-  const uint32_t nsub = (uint32_t)(full_tile_h / tile_h), sub = blockIdx.x % nsub;
+  // a CTA blends a "part" of a semantic tile: all its rows, `part_w` = 32 / nsub of its columns (the
+  // whole tile, or a column strip so that a crowded tile's list is walked by several SMs at
+  // once); parts of one tile are neighbours in the grid.  A warp owns an 8 x 4 pixel block: a splat
+  // a few pixels across then occupies a third of the lanes of the warps it reaches, where a
+  // 32 x 1 pixel row would leave nine lanes in ten idle.
+  const uint32_t nsub = (uint32_t)(32 / part_w), sub = blockIdx.x % nsub;
+  const uint32_t cbn = (uint32_t)part_w / 8u;            // 8-pixel column blocks per part
+  const uint32_t cb = row % cbn, rb = row / cbn;         // `row` = warp index: its block
+  const uint32_t x_local = sub * (uint32_t)part_w + cb * 8u + (lane & 7u), y_local = rb * 4u + (lane >> 3);
+  const bool valid = y_local < (uint32_t)full_tile_h;    // tile heights that are no multiple of 4
   // tiles are taken longest list first (tile_order_kernel) so the long ones do not start last
   const uint32_t tile = order[blockIdx.x / nsub] + (uint32_t)row_begin * tiles_across;
   const uint2 range = ranges[tile];
   const uint32_t n = range.y - range.x;
   const uint32_t part = tile * nsub + sub;
   if (!FIRST && (n == 0 || ts.part_done[part])) return;   // nothing new for this part: its state stands
-  const size_t px = (size_t)tile * (32 * full_tile_h) + (size_t)sub * (32 * tile_h) + tid;
+  // a10 layout: tile-major, row-major inside the tile
+  const size_t px = (size_t)tile * (32 * full_tile_h) + (size_t)(valid ? y_local : 0u) * 32 + x_local;
 
   const uint32_t tcol = tile % tiles_across, trow = tile / tiles_across;
-  const float xf_first = (float)(tcol * 32);
-  const float xf = xf_first + (float)lane;
-  const float ty0 = (float)(trow * full_tile_h + sub * tile_h);
-  const float yf = ty0 + (float)row;
+  const float xp0 = (float)(tcol * 32u + sub * (uint32_t)part_w);   // first pixel column of the part
+  const float xf = (float)(tcol * 32u + x_local);
+  const float ty0 = (float)(trow * full_tile_h);
+  const float yf = ty0 + (float)y_local;
+  const int tile_h = full_tile_h;
 
   float T = 1.f, Cr = 0.f, Cg = 0.f, Cb = 0.f, Ca = 0.f;
-  bool done = false;
-  if (!FIRST) {
+  bool done = !valid;
+  if (!FIRST && valid) {
     const float4 c = fb[px];
     Cr = c.x; Cg = c.y; Cb = c.z; Ca = c.w;
     T = tstate[px];
@@ -105,7 +114,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       const float4 b = __ldg(r + 1);
       const float cb = __ldg(&r[2].x);
       const float A = a.z, B = a.w, C = b.x, op = b.y;
-      uint32_t lo = 1, hi = 0;
+      uint32_t lo = 1, hi = 0, cmask = 0xfu;
       float thr2 = __int_as_float(0x7f800000);   // +inf: never passes
       if (op * 255.0f > 1.0f) {                  // otherwise alpha = op*exp(<=0) < 1/255 everywhere
         const float L2 = __log2f(op * 255.0f);   // power2 >= -L2  <=>  alpha >= 1/255
@@ -123,7 +132,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
           // rows whose minimum already exceeds the bound (with margin) hold no pixel with
           // alpha >= 1/255.  The set of passing rows is an interval (convexity): trim both ends.
           const float bound = 2.0f * 0.6931472f * (L2 + 0.02f) * 1.001f + 1e-4f;
-          const float dxa = a.x - (xf_first + 31.0f), dxb = a.x - xf_first, invA = 1.0f / A;
+          const float dxa = a.x - (xp0 + (float)(part_w - 1)), dxb = a.x - xp0, invA = 1.0f / A;
           auto reaches = [&](uint32_t rrow) {
             const float dy = a.y - (ty0 + (float)rrow);
             const float dx = fminf(fmaxf(-B * dy * invA, dxa), dxb);
@@ -132,12 +141,23 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
           while (lo <= hi && !reaches(lo)) ++lo;
           while (hi > lo && !reaches(hi)) --hi;
           if (lo > hi) { lo = 1; hi = 0; }
+          // the 8-pixel column blocks of the part the ellipse reaches: half-width sqrt(2L * C / det)
+          if (lo <= hi && C > 0.f) {
+            const float hx = sqrtf(2.0f * 0.6931472f * L2 * C / det) * 1.001f + 0.02f;
+            const float fl = ceilf(a.x - hx - xp0), fh = floorf(a.x + hx - xp0);
+            if (fh < 0.f || fl > (float)(part_w - 1)) { lo = 1; hi = 0; }
+            else if (fl == fl && fh == fh) {
+              const uint32_t b0 = fl > 0.f ? (uint32_t)fl >> 3 : 0u;
+              const uint32_t b1 = fh < (float)(part_w - 1) ? (uint32_t)fh >> 3 : (uint32_t)(part_w - 1) >> 3;
+              cmask = ((2u << b1) - 1u) & ~((1u << b0) - 1u);
+            }
+          }
         }
       }
       sA[slot] = make_float4(a.x, a.y, -0.5f * LOG2E * A, -LOG2E * B);
       sB[slot] = make_float4(-0.5f * LOG2E * C, op, b.z, b.w);
       sC[slot] = make_float2(cb, thr2);
-      sRows[slot] = (uint16_t)(lo | (hi << 8));
+      sRows[slot] = (uint16_t)(lo > hi ? 1u : lo | (hi << 5) | (cmask << 10));
     }
     }
     __syncthreads();
@@ -146,7 +166,8 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       for (uint32_t c0 = 0; c0 < m; c0 += 32) {
         const uint32_t jj = c0 + lane;
         uint32_t rr = jj < m ? sRows[jj] : 1u;   // 1 = lo 1, hi 0: empty
-        uint32_t mask = __ballot_sync(0xffffffffu, row >= (rr & 0xffu) && row <= (rr >> 8));
+        uint32_t mask = __ballot_sync(0xffffffffu, (rr & 31u) <= rb * 4u + 3u && ((rr >> 5) & 31u) >= rb * 4u &&
+                                                       ((rr >> (10u + cb)) & 1u));
         // two list entries per turn: their loads, quadratic forms and ex2 overlap; they are then
         // applied to the pixel strictly in list order
         while (mask) {
@@ -197,7 +218,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
     if (__syncthreads_and(done)) break;
   }
   if (!LAST) {
-    tstate[px] = done ? -1.f : T;
+    if (valid) tstate[px] = done ? -1.f : T;
     if (__syncthreads_and(done) && tid == 0) {
       ts.part_done[part] = 1;
       if (atomicAdd(&ts.parts_done[tile], 1u) + 1u == nsub) ts.tile_done[tile] = 1;   // last part of the tile to stop
@@ -217,7 +238,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       atomicAdd(&pair_counters[2 + 2 * (size_t)tile], (unsigned long long)(clock64() - t_begin) / (unsigned)full_tile_h);
     }
   }
-  fb[px] = make_float4(Cr, Cg, Cb, Ca);
+  if (valid) fb[px] = make_float4(Cr, Cg, Cb, Ca);
 }
 
 // ---- launch order of the tiles: longest list first ---------------------------------------------
@@ -298,12 +319,13 @@ static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, cons
   const int rows = fp.row_end - fp.row_begin;
   if (rows <= 0) return;
   const int full_h = (int)fp.tile_h;
-  const int tile_h = full_h / split;   // rows per CTA
-  // dynamic smem sized for this part height so that several CTAs fit per SM
-  const size_t smem = (size_t)tile_h * 32 * BLEND_SMEM_PER_THREAD;
+  const int part_w = 32 / split;                                  // columns per CTA (split is 1, 2 or 4)
+  const int threads = (part_w / 8) * ((full_h + 3) / 4) * 32;    // one warp per 8 x 4 pixel block
+  // dynamic smem sized for this part so that several CTAs fit per SM
+  const size_t smem = (size_t)threads * BLEND_SMEM_PER_THREAD;
   ++g_launches;
-  blend_kernel<COUNT, FIRST, LAST><<<rows * fp.tiles_across * split, tile_h * 32, smem, st>>>(
-      p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, full_h, tile_h, fb_tiled, tstate, ts, order, pair_counters);
+  blend_kernel<COUNT, FIRST, LAST><<<rows * fp.tiles_across * split, threads, smem, st>>>(
+      p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, full_h, part_w, fb_tiled, tstate, ts, order, pair_counters);
 }
 
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,

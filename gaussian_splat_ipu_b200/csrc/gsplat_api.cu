@@ -380,10 +380,10 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     ctx->ts.parts_done = reinterpret_cast<uint32_t *>(ctx->tile_state);
     ctx->ts.tile_done = ctx->tile_state + 4 * T4;
     ctx->ts.part_done = ctx->ts.tile_done + T4;
-    // K5 CTAs per tile: two half-tiles when the tile height allows (GSPLAT_K5_SPLIT overrides)
-    int split = cfg->tile_h % 2 == 0 && cfg->tile_h / 2 >= 4 ? 2 : 1;
+    // K5 CTAs per tile: two 16-column strips (GSPLAT_K5_SPLIT = 1, 2 or 4 overrides)
+    int split = 2;
     if (const char *e = std::getenv("GSPLAT_K5_SPLIT")) split = std::atoi(e);
-    if (split < 1 || split > BLEND_MAX_SPLIT || cfg->tile_h % split) split = 1;
+    if (split != 1 && split != 2 && split != 4) split = 2;
     ctx->blend_split = split;
     if (const char *e = std::getenv("GSPLAT_GRAPHS")) ctx->use_graphs = std::atoi(e) != 0;
     CUC(cudaMalloc(&ctx->tstate, sizeof(float) * px));
