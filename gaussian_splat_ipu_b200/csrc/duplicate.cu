@@ -102,7 +102,9 @@ __device__ __forceinline__ void emit_rect_warp(uint32_t *__restrict__ keys, uint
 
 template <bool CHECK_DONE>
 __global__ void __launch_bounds__(K2_THREADS)
-duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_gauss, const uint32_t *__restrict__ d_count,
+duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted0, const uint32_t *__restrict__ sorted1,
+                 const uint32_t *__restrict__ key_range, uint32_t sort_bpp, uint32_t sort_passes,
+                 const uint32_t *__restrict__ d_count,
                  uint32_t count_cap, int tiles_across, const uint8_t *__restrict__ tile_done,
                  const uint32_t *__restrict__ live_sat, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t capacity,
                  unsigned long long *__restrict__ lookback, uint32_t *__restrict__ ticket,
@@ -118,6 +120,9 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_gauss, const u
   if (tid == 0) { sm.chain = atomicAdd(ticket, 1u); sm.n_big = 0; }
   __syncthreads();
   const uint32_t b = sm.chain;
+  // where the depth sort left its result (it skips the passes above the key range on the device)
+  const uint32_t *__restrict__ sorted_gauss =
+      key_range && rs_result_buffer(key_range, sort_bpp, sort_passes) ? sorted1 : sorted0;
   uint32_t g[K2_ITEMS];
   uint2 rc[K2_ITEMS];
   uint32_t cnt[K2_ITEMS];
@@ -196,7 +201,8 @@ duplicate_kernel(Projected p, const uint32_t *__restrict__ sorted_gauss, const u
                                tile_done, tid & 31);
 }
 
-void launch_duplicate(const Projected &p, const uint32_t *sorted_gauss, const uint32_t *d_count, uint32_t count_cap,
+void launch_duplicate(const Projected &p, const uint32_t *const sorted_gauss[2], const uint32_t *key_range,
+                      uint32_t sort_bits_per_pass, uint32_t sort_passes, const uint32_t *d_count, uint32_t count_cap,
                       int tiles_across, const uint8_t *tile_done, const uint32_t *live_sat, uint32_t *keys, uint32_t *vals,
                       uint32_t capacity, unsigned long long *lookback, uint32_t *ticket, uint32_t *total,
                       uint32_t *overflow, cudaStream_t st) {
@@ -210,11 +216,13 @@ void launch_duplicate(const Projected &p, const uint32_t *sorted_gauss, const ui
   ++g_launches;
   const int grid = ceil_div(count_cap, K2_CHUNK);
   if (tile_done)
-    duplicate_kernel<true><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_gauss, d_count, count_cap, tiles_across,
+    duplicate_kernel<true><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_gauss[0], sorted_gauss[1], key_range,
+                                                                     sort_bits_per_pass, sort_passes, d_count, count_cap, tiles_across,
                                                                      tile_done, live_sat, keys, vals, capacity, lookback,
                                                                      ticket, total, overflow);
   else
-    duplicate_kernel<false><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_gauss, d_count, count_cap, tiles_across,
+    duplicate_kernel<false><<<grid, K2_THREADS, sizeof(K2Smem), st>>>(p, sorted_gauss[0], sorted_gauss[1], key_range,
+                                                                      sort_bits_per_pass, sort_passes, d_count, count_cap, tiles_across,
                                                                       nullptr, nullptr, keys, vals, capacity, lookback,
                                                                       ticket, total, overflow);
 }

@@ -55,7 +55,8 @@ struct StreamSlot {
 enum Scalar { SC_V = 0, SC_OVERFLOW = 1, SC_TICKET0 = 8 /* K2 chain ticket per slice */,
               SC_DS0 = 16 /* duplicates emitted per slice */, SC_NS0 = 24 /* Gaussians selected per slice */,
               SC_SELTICKET0 = 32 /* selection chain ticket per slice */, SC_TAU0 = 40 /* depth-key thresholds */,
-              SC_FRAME_WORDS = 48, SC_N = 48, SC_SORT_N = 49, SC_COUNT = 64 };
+              SC_KRANGE0 = 48 /* {max, max of ~} depth key of each slice's selection (2 words per slice) */,
+              SC_FRAME_WORDS = 64, SC_N = 64, SC_SORT_N = 65, SC_COUNT = 80 };
 
 // A captured frame (CUDA graph): the whole stage sequence of one frame for one slicing mode.  Only
 // K1's camera argument changes from frame to frame; it is refreshed in place before each launch.

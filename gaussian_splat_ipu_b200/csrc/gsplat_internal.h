@@ -144,8 +144,26 @@ constexpr int RS_GRID = 148 * 3;   // CTAs walk RS_TILE-element tiles with a gri
 void sort_plan(int nbits, int &passes, int &bits_per_pass, int max_bits = RS_MAX_BITS);
 // identity_vals: the first digit takes value = element index instead of reading vals[0].
 // returns index (0/1) of the buffer holding the sorted result
+// key_range (optional, device): {max key, max ~key} of the keys, as select.cu accumulates them.
+// Digits above the highest bit in which the keys differ are the same for every key, so their
+// passes are skipped ON THE DEVICE (the launches stay: the frame is a fixed graph).  Skipped passes
+// are always the last ones; the result then sits in buffer rs_result_buffer(...), which the
+// consumer evaluates on the device too (the host's return value assumes no pass was skipped).
 int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,
-                      bool identity_vals, cudaStream_t st, int max_bits = RS_MAX_BITS);
+                      bool identity_vals, cudaStream_t st, int max_bits = RS_MAX_BITS,
+                      const uint32_t *key_range = nullptr);
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t key_range_bits(const uint32_t *key_range) {
+  const uint32_t mx = key_range[0], mn = ~key_range[1];
+  return mx > mn ? 32u - (uint32_t)__clz(mx ^ mn) : 0u;   // no key, or all keys equal: nothing to sort
+}
+// Index (0/1) of the buffer holding the result of a sort of bits [0, passes * bits_per_pass) that
+// started in buffer 0 and skipped the passes above the key range.
+__device__ __forceinline__ uint32_t rs_result_buffer(const uint32_t *key_range, uint32_t bits_per_pass, uint32_t passes) {
+  const uint32_t need = (key_range_bits(key_range) + bits_per_pass - 1u) / bits_per_pass;
+  return (need < passes ? need : passes) & 1u;
+}
+#endif
 
 // Depth-slice selection (select.cu).  tau[s] = depth-key quantile at fractions f[s] of the drawn
 // Gaussians (sampled); launch_select compacts, in index order, the (key, index) pairs of the
@@ -160,7 +178,8 @@ void launch_depth_quantiles(const uint32_t *depth_key, uint32_t n, const SliceFr
                             cudaStream_t st);
 void launch_select(const Projected &p, uint32_t n, const uint32_t *tau_lo, const uint32_t *tau_hi, int tiles_across,
                    const uint32_t *live_sat, uint32_t *keys_out, uint32_t *idx_out, unsigned long long *lookback,
-                   uint32_t *ticket, uint32_t *total_out, cudaStream_t st);
+                   uint32_t *ticket, uint32_t *total_out, uint32_t *key_range /* += {max key, max ~key} */,
+                   cudaStream_t st);
 
 // K2: walks the *d_count (<= count_cap) depth-sorted Gaussians of one slice (sorted_gauss = values
 // of sort A) and emits one (tile id, Gaussian index) pair per tile of each Gaussian's rectangle —
@@ -174,7 +193,10 @@ constexpr int K2_ITEMS = 4;
 constexpr int K2_LOG_CHUNK = 10;
 constexpr int K2_CHUNK = K2_THREADS * K2_ITEMS;   // Gaussians per CTA == per chain link
 static_assert((1 << K2_LOG_CHUNK) == K2_CHUNK, "binary search depth");
-void launch_duplicate(const Projected &p, const uint32_t *sorted_gauss, const uint32_t *d_count, uint32_t count_cap,
+// sorted_gauss[2] + key_range + the depth sort's plan: the buffer the (device-side pass skipping)
+// sort left its result in is chosen on the device; key_range == nullptr: sorted_gauss[0].
+void launch_duplicate(const Projected &p, const uint32_t *const sorted_gauss[2], const uint32_t *key_range,
+                      uint32_t sort_bits_per_pass, uint32_t sort_passes, const uint32_t *d_count, uint32_t count_cap,
                       int tiles_across, const uint8_t *tile_done, const uint32_t *live_sat, uint32_t *keys, uint32_t *vals,
                       uint32_t capacity, unsigned long long *lookback, uint32_t *ticket, uint32_t *total,
                       uint32_t *overflow, cudaStream_t st);

@@ -34,6 +34,13 @@ __device__ __forceinline__ uint32_t num_elems(const uint32_t *d_n, uint32_t cap)
   return n <= cap ? n : 0u;
 }
 
+// Elements a pass has to move: none when its digit lies above the bits in which the keys differ
+// (launch_radix_sort's key_range): the pass is skipped on the device and the data stays where it is.
+__device__ __forceinline__ uint32_t pass_elems(const uint32_t *d_n, uint32_t cap, const uint32_t *key_range, int shift) {
+  if (key_range && shift >= (int)key_range_bits(key_range)) return 0u;
+  return num_elems(d_n, cap);
+}
+
 constexpr int RS_WARPS = RS_THREADS / 32;
 
 // Ranking uses per-thread digit counters in shared memory (no warp votes, no atomics): every
@@ -134,10 +141,10 @@ __device__ __forceinline__ uint32_t rs_rake(uint32_t *cnt, uint32_t w0, uint32_t
 template <int BITS>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ d_n, uint32_t cap, int shift,
-               uint32_t *__restrict__ block_hist, uint32_t stride) {
+               uint32_t *__restrict__ block_hist, uint32_t stride, const uint32_t *__restrict__ key_range) {
   using G = RsGeom<BITS>;
   extern __shared__ __align__(16) uint32_t rs_cnt[];
-  const uint32_t n = num_elems(d_n, cap);
+  const uint32_t n = pass_elems(d_n, cap, key_range, shift);
   const uint32_t ntiles = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
   const uint32_t tid = threadIdx.x;
   const uint32_t tid_off = rs_pad(tid) * 4u;
@@ -182,9 +189,9 @@ rs_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ d
 // ---- exclusive scan of each digit's row over tiles; digit totals -------------------------------
 __global__ void __launch_bounds__(256)
 rs_scan_kernel(uint32_t *__restrict__ block_hist, uint32_t stride, const uint32_t *__restrict__ d_n, uint32_t cap,
-               uint32_t *__restrict__ digit_totals) {
+               uint32_t *__restrict__ digit_totals, const uint32_t *__restrict__ key_range, int shift) {
   __shared__ uint32_t wt[256 / 32 + 1];
-  const uint32_t n = num_elems(d_n, cap);
+  const uint32_t n = pass_elems(d_n, cap, key_range, shift);
   const uint32_t nb = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
   uint32_t *row = block_hist + (size_t)blockIdx.x * stride;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -236,13 +243,13 @@ rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restri
                   uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
                   const uint32_t *__restrict__ d_n, uint32_t cap, int shift,
                   const uint32_t *__restrict__ block_hist, uint32_t stride,
-                  const uint32_t *__restrict__ digit_totals) {
+                  const uint32_t *__restrict__ digit_totals, const uint32_t *__restrict__ key_range) {
   using G = RsGeom<BITS>;
   extern __shared__ __align__(16) uint32_t rs_cnt[];
   unsigned char *cbytes = reinterpret_cast<unsigned char *>(rs_cnt);
   uint2 *stage = reinterpret_cast<uint2 *>(rs_cnt);
   RsTail &tail = *reinterpret_cast<RsTail *>(cbytes + (rs_scatter_smem(BITS) - sizeof(RsTail)));
-  const uint32_t n = num_elems(d_n, cap);
+  const uint32_t n = pass_elems(d_n, cap, key_range, shift);
   const uint32_t ntiles = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t tid_off = rs_pad(tid) * 4u;
@@ -323,7 +330,7 @@ void sort_plan(int nbits, int &passes, int &bits_per_pass, int max_bits) {
 
 template <int BITS>
 static void launch_pass(SortBuffers &sb, int cur, bool identity, const uint32_t *d_n, int shift, uint32_t grid,
-                        cudaStream_t st) {
+                        const uint32_t *key_range, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(rs_scatter_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -333,15 +340,16 @@ static void launch_pass(SortBuffers &sb, int cur, bool identity, const uint32_t 
     attr_set = true;
   }
   rs_hist_kernel<BITS><<<grid, RS_THREADS, rs_counter_words(BITS) * 4, st>>>(sb.keys[cur], d_n, sb.capacity, shift,
-                                                                            sb.block_hist, sb.max_tiles);
-  rs_scan_kernel<<<1u << BITS, 256, 0, st>>>(sb.block_hist, sb.max_tiles, d_n, sb.capacity, sb.digit_totals);
+                                                                            sb.block_hist, sb.max_tiles, key_range);
+  rs_scan_kernel<<<1u << BITS, 256, 0, st>>>(sb.block_hist, sb.max_tiles, d_n, sb.capacity, sb.digit_totals, key_range,
+                                             shift);
   rs_scatter_kernel<BITS><<<grid, RS_THREADS, rs_scatter_smem(BITS), st>>>(
       sb.keys[cur], identity ? nullptr : sb.vals[cur], sb.keys[cur ^ 1], sb.vals[cur ^ 1], d_n, sb.capacity, shift,
-      sb.block_hist, sb.max_tiles, sb.digit_totals);
+      sb.block_hist, sb.max_tiles, sb.digit_totals, key_range);
 }
 
 int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,
-                      bool identity_vals, cudaStream_t st, int max_bits) {
+                      bool identity_vals, cudaStream_t st, int max_bits, const uint32_t *key_range) {
   if (n_upper > sb.capacity) n_upper = sb.capacity;
   const uint32_t ntiles = (uint32_t)(((uint64_t)n_upper + RS_TILE - 1) / RS_TILE);
   int cur = 0;
@@ -355,14 +363,14 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
     const bool ident = p == 0 && identity_vals;
     g_launches += 3;
     switch (bits) {
-      case 1: launch_pass<1>(sb, cur, ident, d_n, shift, grid, st); break;
-      case 2: launch_pass<2>(sb, cur, ident, d_n, shift, grid, st); break;
-      case 3: launch_pass<3>(sb, cur, ident, d_n, shift, grid, st); break;
-      case 4: launch_pass<4>(sb, cur, ident, d_n, shift, grid, st); break;
-      case 5: launch_pass<5>(sb, cur, ident, d_n, shift, grid, st); break;
-      case 6: launch_pass<6>(sb, cur, ident, d_n, shift, grid, st); break;
-      case 7: launch_pass<7>(sb, cur, ident, d_n, shift, grid, st); break;
-      default: launch_pass<8>(sb, cur, ident, d_n, shift, grid < 148u ? grid : 148u, st); break;
+      case 1: launch_pass<1>(sb, cur, ident, d_n, shift, grid, key_range, st); break;
+      case 2: launch_pass<2>(sb, cur, ident, d_n, shift, grid, key_range, st); break;
+      case 3: launch_pass<3>(sb, cur, ident, d_n, shift, grid, key_range, st); break;
+      case 4: launch_pass<4>(sb, cur, ident, d_n, shift, grid, key_range, st); break;
+      case 5: launch_pass<5>(sb, cur, ident, d_n, shift, grid, key_range, st); break;
+      case 6: launch_pass<6>(sb, cur, ident, d_n, shift, grid, key_range, st); break;
+      case 7: launch_pass<7>(sb, cur, ident, d_n, shift, grid, key_range, st); break;
+      default: launch_pass<8>(sb, cur, ident, d_n, shift, grid < 148u ? grid : 148u, key_range, st); break;
     }
     cur ^= 1;
   }

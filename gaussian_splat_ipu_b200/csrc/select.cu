@@ -109,8 +109,9 @@ select_kernel(const uint32_t *__restrict__ depth_key, const uint2 *__restrict__ 
               const uint32_t *__restrict__ tau_lo /* nullptr: 0 */, const uint32_t *__restrict__ tau_hi /* nullptr: all drawn */,
               int tiles_across, const uint32_t *__restrict__ live_sat, uint32_t *__restrict__ keys_out,
               uint32_t *__restrict__ idx_out, unsigned long long *__restrict__ lookback, uint32_t *__restrict__ ticket,
-              uint32_t *__restrict__ total_out) {
+              uint32_t *__restrict__ total_out, uint32_t *__restrict__ key_range /* {max key, max ~key} */) {
   __shared__ uint32_t wc[SEL_ITEMS * (SEL_THREADS / 32) + 1];
+  __shared__ uint32_t wmax[2 * (SEL_THREADS / 32)];
   __shared__ uint32_t chain_s;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) chain_s = atomicAdd(ticket, 1u);
@@ -127,6 +128,7 @@ select_kernel(const uint32_t *__restrict__ depth_key, const uint2 *__restrict__ 
     key[k] = i < n ? depth_key[i] : DEPTH_KEY_CULLED;
   }
   uint32_t sel = 0;   // bit k: item k is selected
+  uint32_t kmax = 0u, kinv = 0u;
 #pragma unroll
   for (int k = 0; k < SEL_ITEMS; ++k) {
     bool take = key[k] >= lo && key[k] < hi;   // hi <= DEPTH_KEY_CULLED: culled Gaussians never pass
@@ -137,8 +139,19 @@ select_kernel(const uint32_t *__restrict__ depth_key, const uint2 *__restrict__ 
     sel |= take ? (1u << k) : 0u;
     const uint32_t m = __ballot_sync(0xffffffffu, take);
     if (lane == 0) wc[k * (SEL_THREADS / 32) + warp] = __popc(m);
+    if (take) { kmax = max(kmax, key[k]); kinv = max(kinv, ~key[k]); }
   }
+  // range of the selected keys: the depth sort skips the digits above the bits in which they differ
+  kmax = __reduce_max_sync(0xffffffffu, kmax);
+  kinv = __reduce_max_sync(0xffffffffu, kinv);
+  if (lane == 0) { wmax[warp] = kmax; wmax[SEL_THREADS / 32 + warp] = kinv; }
   __syncthreads();
+  if (tid < 2 * (SEL_THREADS / 32)) {   // lanes 0-7: max key, lanes 8-15: max ~key
+    uint32_t v = wmax[tid];
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0x0000ffffu, v, o));
+    if ((tid & 7u) == 0 && v) atomicMax(&key_range[tid >> 3], v);
+  }
   // exclusive scan of the SEL_ITEMS x warps counts in (k, warp) order: one warp, 4 entries per lane
   constexpr int NWC = SEL_ITEMS * (SEL_THREADS / 32);
   static_assert(NWC == 128, "one warp scans 4 entries per lane");
@@ -183,16 +196,16 @@ select_kernel(const uint32_t *__restrict__ depth_key, const uint2 *__restrict__ 
 
 void launch_select(const Projected &p, uint32_t n, const uint32_t *tau_lo, const uint32_t *tau_hi, int tiles_across,
                    const uint32_t *live_sat, uint32_t *keys_out, uint32_t *idx_out, unsigned long long *lookback,
-                   uint32_t *ticket, uint32_t *total_out, cudaStream_t st) {
+                   uint32_t *ticket, uint32_t *total_out, uint32_t *key_range, cudaStream_t st) {
   if (!n) return;
   ++g_launches;
   const int grid = ceil_div(n, SEL_CHUNK);
   if (live_sat)
     select_kernel<true><<<grid, SEL_THREADS, 0, st>>>(p.depth_key, p.rect, n, tau_lo, tau_hi, tiles_across, live_sat,
-                                                      keys_out, idx_out, lookback, ticket, total_out);
+                                                      keys_out, idx_out, lookback, ticket, total_out, key_range);
   else
     select_kernel<false><<<grid, SEL_THREADS, 0, st>>>(p.depth_key, p.rect, n, tau_lo, tau_hi, tiles_across, nullptr,
-                                                       keys_out, idx_out, lookback, ticket, total_out);
+                                                       keys_out, idx_out, lookback, ticket, total_out, key_range);
 }
 
 }  // namespace gsplat
