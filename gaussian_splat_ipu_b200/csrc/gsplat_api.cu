@@ -56,7 +56,8 @@ enum Scalar { SC_V = 0, SC_OVERFLOW = 1, SC_TICKET0 = 8 /* K2 chain ticket per s
               SC_DS0 = 16 /* duplicates emitted per slice */, SC_NS0 = 24 /* Gaussians selected per slice */,
               SC_SELTICKET0 = 32 /* selection chain ticket per slice */, SC_TAU0 = 40 /* depth-key thresholds */,
               SC_KRANGE0 = 48 /* {max, max of ~} depth key of each slice's selection (2 words per slice) */,
-              SC_FRAME_WORDS = 64, SC_N = 64, SC_SORT_N = 65, SC_COUNT = 80 };
+              SC_FRAME_WORDS = 64 };
+enum Persist { P_N = 0 /* scene size */, P_SORT_N = 1 /* gsplat_sort_pairs count */, P_COUNT = 16 };
 
 // A captured frame (CUDA graph): the whole stage sequence of one frame for one slicing mode.  Only
 // K1's camera argument changes from frame to frame; it is refreshed in place before each launch.
@@ -108,7 +109,15 @@ struct gsplat_ctx {
   uint64_t auto_frames = 0, mode_frames[2] = {0, 0};
   SliceFractions slice_fr{};       // cumulative fractions of the thresholds (num_slices - 1 of them)
   unsigned long long *sel_lookback = nullptr;   // selection chains, one per slice
-  uint8_t *tile_state = nullptr;   // one block, zeroed per frame: TileState arrays
+  // Everything that is zeroed at the start of every frame sits in two blocks so that a frame starts
+  // with two memsets instead of six (each one is a node on the frame's critical path):
+  //   frame_block (create): device scalars [0, SC_FRAME_WORDS) | TileState arrays | ranges of every slice
+  //   chain_block (upload): look-back words of K2 and of the selection, every slice
+  uint8_t *frame_block = nullptr, *chain_block = nullptr;
+  size_t frame_block_bytes = 0, chain_block_bytes = 0;
+  uint32_t *d_persist = nullptr;   // device scalars that outlive a frame (enum Persist)
+  uint2 *ranges_last = nullptr;    // ranges of the last slice of the last frame
+  uint8_t *tile_state = nullptr;   // inside frame_block: TileState arrays
   TileState ts{};                  // per tile / per part: every pixel has stopped
   int blend_split = 1;             // K5 CTAs per semantic tile
   // frame graphs: [0] one slice, [1] sliced; dropped whenever buffers, scene or band change
@@ -264,11 +273,11 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   drop_graphs(ctx);
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
   dfree(ctx->proj.rec); dfree(ctx->proj.rect);
-  dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->d_scalars); dfree(ctx->lookback);
-  dfree(ctx->sel_lookback); dfree(ctx->proj.depth_key);
+  dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->frame_block); dfree(ctx->d_persist); dfree(ctx->chain_block);
+  dfree(ctx->proj.depth_key);
   free_sort(ctx->sort_a); free_sort(ctx->sort_b);
-  dfree(ctx->ranges); dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
-  dfree(ctx->count_diff); dfree(ctx->live_sat); dfree(ctx->tile_order); dfree(ctx->tile_state); dfree(ctx->tstate);
+  dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
+  dfree(ctx->count_diff); dfree(ctx->live_sat); dfree(ctx->tile_order); dfree(ctx->tstate);
   if (ctx->copy_st) cudaStreamSynchronize(ctx->copy_st);
   for (auto &ss : ctx->sslots) {
     dfree(ss.d_bgr); dfree(ss.d_counts);
@@ -355,28 +364,33 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   CUC(cudaEventCreate(&ctx->t1));
   CUC(cudaEventCreate(&ctx->post0));
   CUC(cudaEventCreate(&ctx->post1));
-  CUC(cudaMalloc(&ctx->d_scalars, SC_COUNT * sizeof(uint32_t)));
-  CUC(cudaMemset(ctx->d_scalars, 0, SC_COUNT * sizeof(uint32_t)));
+  {
+    const size_t tsb = (tile_state_bytes(ctx->num_tiles) + 15) / 16 * 16;
+    ctx->frame_block_bytes = SC_FRAME_WORDS * sizeof(uint32_t) + tsb + (size_t)MAX_SLICES * ctx->num_tiles * sizeof(uint2);
+    CUC(cudaMalloc(&ctx->frame_block, ctx->frame_block_bytes));
+    CUC(cudaMemset(ctx->frame_block, 0, ctx->frame_block_bytes));
+    ctx->d_scalars = reinterpret_cast<uint32_t *>(ctx->frame_block);
+    ctx->tile_state = ctx->frame_block + SC_FRAME_WORDS * sizeof(uint32_t);
+    ctx->ranges = reinterpret_cast<uint2 *>(ctx->tile_state + tsb);
+    ctx->ranges_last = ctx->ranges;
+    CUC(cudaMalloc(&ctx->d_persist, P_COUNT * sizeof(uint32_t)));
+    CUC(cudaMemset(ctx->d_persist, 0, P_COUNT * sizeof(uint32_t)));
+  }
   ctx->tile_bits = ceil_log2((uint32_t)ctx->num_tiles);
   if (ctx->tile_bits < 1) ctx->tile_bits = 1;
   const size_t px = (size_t)cfg->width * cfg->height;
-  CUC(cudaMalloc(&ctx->ranges, sizeof(uint2) * ctx->num_tiles));
   CUC(cudaMalloc(&ctx->counts, sizeof(uint32_t) * ctx->num_tiles));
   CUC(cudaMalloc(&ctx->fb, sizeof(float4) * px));
   CUC(cudaMalloc(&ctx->bgr, px * 3));
   CUC(cudaMemset(ctx->fb, 0, sizeof(float4) * px));
   CUC(cudaMemset(ctx->bgr, 0, px * 3));
   CUC(cudaMemset(ctx->counts, 0, sizeof(uint32_t) * ctx->num_tiles));
-  CUC(cudaMemset(ctx->ranges, 0, sizeof(uint2) * ctx->num_tiles));
   {
     const size_t grid = (size_t)(ctx->tiles_across + 1) * (ctx->tiles_down + 1);
     CUC(cudaMalloc(&ctx->live_sat, sizeof(uint32_t) * grid));
     CUC(cudaMalloc(&ctx->tile_order, sizeof(uint32_t) * ctx->num_tiles));
     CUC(cudaMalloc(&ctx->count_diff, sizeof(int) * grid));
     CUC(cudaMemset(ctx->count_diff, 0, sizeof(int) * grid));
-    const size_t tsb = tile_state_bytes(ctx->num_tiles);
-    CUC(cudaMalloc(&ctx->tile_state, tsb));
-    CUC(cudaMemset(ctx->tile_state, 0, tsb));
     const size_t T4 = ((size_t)ctx->num_tiles + 3) / 4 * 4;
     ctx->ts.parts_done = reinterpret_cast<uint32_t *>(ctx->tile_state);
     ctx->ts.tile_done = ctx->tile_state + 4 * T4;
@@ -402,8 +416,8 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   drop_graphs(ctx);
   for (auto &sl : ctx->slots) sl.pending = false;
   dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
-  dfree(ctx->proj.rec); dfree(ctx->proj.rect); dfree(ctx->lookback);
-  dfree(ctx->sel_lookback); dfree(ctx->proj.depth_key);
+  dfree(ctx->proj.rec); dfree(ctx->proj.rect); dfree(ctx->chain_block);
+  dfree(ctx->proj.depth_key);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4);
   ctx->have_scene = ctx->have_frame = false;
   const size_t na = n ? n : 1;
@@ -416,9 +430,11 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   CU(cudaMemsetAsync(ctx->proj.rec, 0, na * 3 * sizeof(float4), ctx->st));
   CU(cudaMalloc(&ctx->proj.rect, na * sizeof(uint2)));
   ctx->n_blocks = (uint32_t)((n + K2_CHUNK - 1) / K2_CHUNK);
-  CU(cudaMalloc(&ctx->lookback, (size_t)MAX_SLICES * (ctx->n_blocks + 1) * sizeof(unsigned long long)));
   ctx->n_sel_blocks = (uint32_t)((n + 4095) / 4096);
-  CU(cudaMalloc(&ctx->sel_lookback, (size_t)MAX_SLICES * (ctx->n_sel_blocks + 1) * sizeof(unsigned long long)));
+  ctx->chain_block_bytes = (size_t)MAX_SLICES * ((size_t)ctx->n_blocks + ctx->n_sel_blocks + 2) * sizeof(unsigned long long);
+  CU(cudaMalloc(&ctx->chain_block, ctx->chain_block_bytes));
+  ctx->lookback = reinterpret_cast<unsigned long long *>(ctx->chain_block);
+  ctx->sel_lookback = ctx->lookback + (size_t)MAX_SLICES * (ctx->n_blocks + 1);
   CU(cudaMalloc(&ctx->proj.depth_key, na * sizeof(uint32_t)));
   plan_slices(ctx);
   if (ctx->cfg.debug_records) {
@@ -429,7 +445,7 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
     int rc = alloc_sort(ctx, ctx->sort_a, n);
     if (rc) return rc;
     const uint32_t n32 = (uint32_t)n;
-    CU(cudaMemcpyAsync(ctx->d_scalars + SC_N, &n32, 4, cudaMemcpyHostToDevice, ctx->st));
+    CU(cudaMemcpyAsync(ctx->d_persist + P_N, &n32, 4, cudaMemcpyHostToDevice, ctx->st));
     CU(cudaStreamSynchronize(ctx->st));
   }
   if (n) {
