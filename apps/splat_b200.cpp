@@ -243,6 +243,7 @@ int main(int argc, char **argv) {
     const std::uint8_t *bgr = nullptr;
     const std::uint32_t *counts = nullptr;
     std::vector<std::uint64_t> inflight;
+    const std::size_t depth = 2 * (std::size_t)s.concurrentFrames();   // tickets outstanding: two per frame in flight
     unsigned long long pixel_sum = 0, count_sum = 0;
     auto deliver = [&](std::uint64_t ticket) {   // what the AsyncTask thread does with imagePtrBuffered
       s.acquireFrame(ticket, &bgr, &counts);
@@ -255,7 +256,7 @@ int main(int argc, char **argv) {
       // config 2 orbit: glm::rotate(mvpStart, radians(360 / frames * k), (0,1,0))
       s.updateModelView(rotate(base, (360.0f / (float)frames * (float)k) * 0.017453292519943295f, {0.f, 1.f, 0.f}));
       inflight.push_back(s.executeStreamed());
-      if (inflight.size() > 2) { deliver(inflight.front()); inflight.erase(inflight.begin()); }
+      if (inflight.size() > depth) { deliver(inflight.front()); inflight.erase(inflight.begin()); }
     }
     while (!inflight.empty()) { deliver(inflight.front()); inflight.erase(inflight.begin()); }
     const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();

@@ -86,6 +86,11 @@ struct gsplat_ctx {
   uint32_t *d_scalars = nullptr;
   uint32_t *h_scalars = nullptr;   // pinned, NUM_SLOTS * 4 words
   // sort A: Gaussians by depth (capacity N); sort B: duplicates by tile (capacity grows)
+  // Frames in flight (gsplat_config.concurrent_frames > 1): this context is then only a dispatcher
+  // over `lanes` complete contexts (own stream, own buffers, own copy of the scene) that take
+  // the frames round-robin; result reads go to the lane of the frame rendered last.
+  std::vector<gsplat_ctx *> lanes;
+  int next_lane = 0, last_lane = 0;
   SortBuffers sort_a{}, sort_b{};
   int sorted_a = 0, sorted = 0;    // which of sort_x.keys/vals holds the sorted result
   unsigned long long *lookback = nullptr;
@@ -249,6 +254,28 @@ void mat4_mul(const float *a, const float *b, float *r) {
 
 extern "C" {
 
+// ---- frames in flight: routing of the C ABI over the lanes of a dispatcher context ---------------
+// ROUTE_LAST: the call refers to the frame rendered last (reads, stats, parity taps).
+// ROUTE_ALL:  the call sets state every lane needs (scene, camera, band) or waits for all of them.
+#define ROUTE_LAST(call)                                              \
+  if (ctx && !ctx->lanes.empty()) {                                   \
+    gsplat_ctx *outer_ = ctx;                                         \
+    ctx = outer_->lanes[outer_->last_lane];                           \
+    const int rc_ = (call);                                           \
+    if (rc_ < 0) outer_->err = ctx->err;                              \
+    return rc_;                                                       \
+  }
+#define ROUTE_ALL(call)                                               \
+  if (ctx && !ctx->lanes.empty()) {                                   \
+    gsplat_ctx *outer_ = ctx;                                         \
+    for (gsplat_ctx *lane_ : outer_->lanes) {                         \
+      ctx = lane_;                                                    \
+      const int rc_ = (call);                                         \
+      if (rc_ < 0) { outer_->err = lane_->err; return rc_; }          \
+    }                                                                 \
+    return GSPLAT_OK;                                                 \
+  }
+
 int gsplat_abi_version(void) { return GSPLAT_ABI_VERSION; }
 
 int gsplat_config_default(gsplat_config *cfg) {
@@ -265,6 +292,11 @@ const char *gsplat_last_error(const gsplat_ctx *ctx) { return ctx ? ctx->err.c_s
 
 void gsplat_destroy(gsplat_ctx *ctx) {
   if (!ctx) return;
+  if (!ctx->lanes.empty()) {
+    for (gsplat_ctx *lane : ctx->lanes) gsplat_destroy(lane);
+    delete ctx;
+    return;
+  }
   if (std::getenv("GSPLAT_DEBUG"))
     std::fprintf(stderr, "[gsplat] auto=%d frames one-slice %llu (%.3f ms) sliced %llu (%.3f ms)\n", (int)ctx->auto_slices,
                  (unsigned long long)ctx->mode_frames[0], ctx->ema_ms[0], (unsigned long long)ctx->mode_frames[1], ctx->ema_ms[1]);
@@ -326,6 +358,37 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     return fail(nullptr, GSPLAT_E_CUDA, std::string("gsplat_create: no CUDA device (there is no CPU fallback): ") +
                                             cudaGetErrorString(e));
   if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: bad device ordinal");
+  if (cfg->concurrent_frames < 0 || cfg->concurrent_frames > GSPLAT_MAX_CONCURRENT_FRAMES)
+    return fail(nullptr, GSPLAT_E_ARG, "gsplat_create: concurrent_frames must be 0 (default) .. GSPLAT_MAX_CONCURRENT_FRAMES");
+  {
+    int nl = cfg->concurrent_frames;
+    if (nl == 0) {
+      if (cfg->collect_timings || cfg->debug_records) nl = 1;   // stage events and parity taps describe ONE frame at a time
+      else {
+        nl = GSPLAT_DEFAULT_CONCURRENT_FRAMES;
+        if (const char *e2 = std::getenv("GSPLAT_CONCURRENT_FRAMES")) nl = std::atoi(e2);   // experiments
+        if (nl < 1 || nl > GSPLAT_MAX_CONCURRENT_FRAMES) nl = 1;
+      }
+    }
+    if (nl > 1) {
+      gsplat_ctx *outer = new gsplat_ctx;
+      outer->cfg = *cfg;
+      gsplat_config lane_cfg = *cfg;
+      lane_cfg.concurrent_frames = 1;
+      for (int l = 0; l < nl; ++l) {
+        gsplat_ctx *lane = nullptr;
+        const int rc = gsplat_create(&lane_cfg, &lane);
+        if (rc) {   // g_create_error is the lane's
+          for (gsplat_ctx *made : outer->lanes) gsplat_destroy(made);
+          delete outer;
+          return rc;
+        }
+        outer->lanes.push_back(lane);
+      }
+      *out = outer;
+      return GSPLAT_OK;
+    }
+  }
   ctx = new gsplat_ctx;
   ctx->cfg = *cfg;
   ctx->tiles_across = cfg->width / cfg->tile_w;
@@ -409,6 +472,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
 }
 
 int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
+  ROUTE_ALL(gsplat_upload_scene(ctx, g16, n));
   if (!ctx || (!g16 && n)) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: null argument");
   if (n > 0x7fffffffull) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: too many Gaussians");
   CU(cudaSetDevice(ctx->cfg.device));
@@ -469,6 +533,7 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
 }
 
 int gsplat_set_camera(gsplat_ctx *ctx, const float mv[16], const float proj[16], float fov, float scale_div) {
+  ROUTE_ALL(gsplat_set_camera(ctx, mv, proj, fov, scale_div));
   if (!ctx || !mv || !proj) return fail(ctx, GSPLAT_E_ARG, "gsplat_set_camera: null argument");
   FrameParams &fp = ctx->fp;
   // codelets.cpp:443: mvp = projmatrix * viewmatrix (the host-side transpose of
@@ -491,6 +556,7 @@ int gsplat_set_camera(gsplat_ctx *ctx, const float mv[16], const float proj[16],
 }
 
 int gsplat_set_band(gsplat_ctx *ctx, int row_begin, int row_end) {
+  ROUTE_ALL(gsplat_set_band(ctx, row_begin, row_end));
   if (!ctx) return GSPLAT_E_ARG;
   if (row_begin < 0 || row_end > ctx->tiles_down || row_begin > row_end)
     return fail(ctx, GSPLAT_E_ARG, "gsplat_set_band: bad tile-row band");

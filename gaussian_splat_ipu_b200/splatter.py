@@ -33,7 +33,7 @@ class Config(C.Structure):
     _fields_ = [("device", C.c_int), ("width", C.c_int), ("height", C.c_int), ("tile_w", C.c_int),
                 ("tile_h", C.c_int), ("guard_factor", C.c_float), ("band_row_begin", C.c_int),
                 ("band_row_end", C.c_int), ("collect_timings", C.c_int), ("debug_records", C.c_int),
-                ("dup_capacity", C.c_size_t), ("depth_slices", C.c_int)]
+                ("dup_capacity", C.c_size_t), ("depth_slices", C.c_int), ("concurrent_frames", C.c_int)]
 
 
 class FrameStats(C.Structure):
@@ -77,6 +77,7 @@ SYMBOLS = {
     "gsplat_timer_begin": (C.c_int, [_vp]),
     "gsplat_timer_end": (C.c_int, [_vp, _fp]),
     "gsplat_launch_count": (C.c_uint64, []),
+    "gsplat_concurrent_frames": (C.c_int, [_vp]),
     "gsplat_count_pairs": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
 }
 
@@ -159,7 +160,8 @@ class B200Splatter:
     ``getIPUHistogram``."""
 
     def __init__(self, gaussians16: np.ndarray, width=1280, height=720, tile_w=32, tile_h=20, device=0,
-                 band=None, collect_timings=False, debug_records=False, dup_capacity=0, depth_slices=0):
+                 band=None, collect_timings=False, debug_records=False, dup_capacity=0, depth_slices=0,
+                 concurrent_frames=0):
         self.lib = load_library()
         cfg = Config()
         self.lib.gsplat_config_default(C.byref(cfg))
@@ -168,6 +170,7 @@ class B200Splatter:
             cfg.band_row_begin, cfg.band_row_end = band
         cfg.collect_timings, cfg.debug_records, cfg.dup_capacity = int(collect_timings), int(debug_records), dup_capacity
         cfg.depth_slices = int(depth_slices)   # 0 = library default; 1 = complete (reference) lists
+        cfg.concurrent_frames = int(concurrent_frames)   # 0 = library default (2 frames in flight on the device)
         self.cfg = cfg
         self.h = _vp()
         rc = self.lib.gsplat_create(C.byref(cfg), C.byref(self.h))
@@ -184,6 +187,11 @@ class B200Splatter:
         g = np.ascontiguousarray(gaussians16, dtype=np.float32).reshape(-1, 16)
         self.n = g.shape[0]
         self._check(self.lib.gsplat_upload_scene(self.h, g.ctypes.data_as(_fp), self.n))
+
+    @property
+    def concurrent_frames(self) -> int:
+        """Frames the context keeps in flight on the device (lanes taking the frames round-robin)."""
+        return int(self.lib.gsplat_concurrent_frames(self.h))
 
     # -- plumbing
     def _check(self, rc):

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define GSPLAT_ABI_VERSION 2
+#define GSPLAT_ABI_VERSION 3
 
 typedef enum gsplat_status {
   GSPLAT_OK = 0,
@@ -63,7 +63,16 @@ typedef struct gsplat_config {
                          /* 1 = one slice: every tile's list is the reference's complete list.  */
                          /* 0 = default (GSPLAT_DEFAULT_DEPTH_SLICES).  Framebuffer and counts   */
                          /* do not depend on it; lists are exact prefixes of the reference's.   */
+  int concurrent_frames; /* frames the context keeps in flight on the device (1..4): the frame is a */
+                         /* chain of short, latency-bound launches, so consecutive frames run on    */
+                         /* separate streams with their own working buffers ("lanes", round-robin)  */
+                         /* and interleave on the SMs.  Every call that reads a result refers to    */
+                         /* the frame rendered last.  0 = default: GSPLAT_DEFAULT_CONCURRENT_FRAMES, */
+                         /* or 1 when collect_timings / debug_records are set.  Costs one set of    */
+                         /* buffers (about 250 bytes per Gaussian) per frame in flight.             */
 } gsplat_config;
+#define GSPLAT_MAX_CONCURRENT_FRAMES 4
+#define GSPLAT_DEFAULT_CONCURRENT_FRAMES 3
 #define GSPLAT_MAX_DEPTH_SLICES 8
 #define GSPLAT_DEFAULT_DEPTH_SLICES 2
 
@@ -137,6 +146,10 @@ int gsplat_read_tile_counts(gsplat_ctx *ctx, uint32_t *dst);
 #define GSPLAT_STREAM_SLOTS 3
 int gsplat_render_streamed(gsplat_ctx *ctx, uint64_t *ticket);
 int gsplat_acquire_frame(gsplat_ctx *ctx, uint64_t ticket, const uint8_t **bgr8, const uint32_t **counts);
+/* Frames this context keeps in flight on the device (gsplat_config.concurrent_frames resolved).
+ * A streaming caller gets full overlap with 2 tickets outstanding per frame in flight
+ * (GSPLAT_STREAM_SLOTS - 1 each is the limit). */
+int gsplat_concurrent_frames(const gsplat_ctx *ctx);
 
 typedef struct gsplat_frame_stats {
   uint64_t num_gaussians; /* N                                             */

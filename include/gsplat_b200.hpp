@@ -113,6 +113,9 @@ public:
     check(gsplat_acquire_frame(ctx_, ticket, bgr, counts));
   }
 
+  // frames the context keeps in flight on the device (gsplat_config.concurrent_frames resolved)
+  int concurrentFrames() const { return gsplat_concurrent_frames(ctx_); }
+
   // multi-GPU tile bands (no reference equivalent: single IPU, src/main/splat.cpp:41-46)
   void setBand(int rowBegin, int rowEnd) { check(gsplat_set_band(ctx_, rowBegin, rowEnd)); }
   gsplat_frame_stats stats() const {

@@ -40,7 +40,7 @@ def test_library_exports_every_declared_symbol():
 def test_ctypes_mirror_binds_the_declared_set():
     assert sorted(sp.SYMBOLS) == declared_symbols()
     lib = sp.load_library()
-    assert lib.gsplat_abi_version() == 2
+    assert lib.gsplat_abi_version() == 3
 
 
 def test_config_defaults_are_the_reference_constants():
