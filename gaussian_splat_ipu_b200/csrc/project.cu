@@ -133,7 +133,10 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
       px += 0.0f; py += 0.0f;
       cz = clip[2];
       // g.scale = g.scale / fxy[1], codelets.cpp:463
-      const float sc0 = p.w / fp.scale_div, sc1 = s12.x / fp.scale_div, sc2 = s12.y / fp.scale_div;
+      // g.scale / fxy[1] (codelets.cpp:463); x / 1.0f is x exactly, and an IEEE division is ~12
+      // instructions: skip the three of them for the true-scale divisor (uniform branch)
+      float sc0 = p.w, sc1 = s12.x, sc2 = s12.y;
+      if (fp.scale_div != 1.0f) { sc0 = sc0 / fp.scale_div; sc1 = sc1 / fp.scale_div; sc2 = sc2 / fp.scale_div; }
 
       // ---- Gaussian3D::ComputeCov3D, ipu_geometry.hpp:315-323 (glm normalize + mat3_cast)
       float w = q.x, x = q.y, y = q.z, z = q.w;
