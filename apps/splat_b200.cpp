@@ -5,7 +5,7 @@
 // frame as a PPM and print the frame rate.  No Boost / OpenCV / spdlog / Poplar: plain C++17.
 //
 //   splat_b200 --input scene.ply [--width 1280] [--height 720] [--frames 32] [--scale-div 0.1]
-//              [--out frame.ppm] [--device 0]
+//              [--out frame.ppm] [--device 0] [--cache scene.gsc]
 //   splat_b200 --synthetic 1000000 ...          (SURVEY §8d generator instead of a PLY)
 //
 // What replaces what (reference file:line):
@@ -204,6 +204,39 @@ const char *arg(int argc, char **argv, const char *name, const char *dflt) {
 
 }  // namespace
 
+// ---- scene cache ---------------------------------------------------------------
+// The converted scene — Gaussian3D records after the PLY -> record conversion and the app's
+// recentre + z-negate — as one flat file, so that a restart skips PLY parsing and conversion:
+//   "GSPLB200" | u32 version (1) | u32 0 | u64 n | f32 bbox min[3], max[3] | n x 16 f32 records
+// (little-endian; gaussian_splat_ipu_b200/scene.py reads and writes the same file).
+static bool cache_write(const std::string &path, const std::vector<splat::Gaussian3DRecord> &g, Vec3 bmin, Vec3 bmax) {
+  std::FILE *f = std::fopen(path.c_str(), "wb");
+  if (!f) return false;
+  const std::uint32_t ver[2] = {1u, 0u};
+  const std::uint64_t n = g.size();
+  const float bb[6] = {bmin.x, bmin.y, bmin.z, bmax.x, bmax.y, bmax.z};
+  bool ok = std::fwrite("GSPLB200", 1, 8, f) == 8 && std::fwrite(ver, 4, 2, f) == 2 && std::fwrite(&n, 8, 1, f) == 1 &&
+            std::fwrite(bb, 4, 6, f) == 6 && std::fwrite(g.data(), sizeof(splat::Gaussian3DRecord), g.size(), f) == g.size();
+  return std::fclose(f) == 0 && ok;
+}
+static bool cache_read(const std::string &path, std::vector<splat::Gaussian3DRecord> &g, Vec3 &bmin, Vec3 &bmax) {
+  std::FILE *f = std::fopen(path.c_str(), "rb");
+  if (!f) return false;
+  char magic[8];
+  std::uint32_t ver[2];
+  std::uint64_t n = 0;
+  float bb[6];
+  bool ok = std::fread(magic, 1, 8, f) == 8 && !std::memcmp(magic, "GSPLB200", 8) && std::fread(ver, 4, 2, f) == 2 &&
+            ver[0] == 1u && std::fread(&n, 8, 1, f) == 1 && std::fread(bb, 4, 6, f) == 6;
+  if (ok) {
+    g.resize((std::size_t)n);
+    ok = std::fread(g.data(), sizeof(splat::Gaussian3DRecord), g.size(), f) == g.size();
+    bmin = {bb[0], bb[1], bb[2]}; bmax = {bb[3], bb[4], bb[5]};
+  }
+  std::fclose(f);
+  return ok;
+}
+
 int main(int argc, char **argv) {
   const std::string input = arg(argc, argv, "--input", "");
   const std::size_t synthetic = std::strtoull(arg(argc, argv, "--synthetic", "0"), nullptr, 10);
@@ -212,9 +245,10 @@ int main(int argc, char **argv) {
   const float scale_div = (float)std::atof(arg(argc, argv, "--scale-div", synthetic ? "1.0" : "0.1"));   // lambda1/10, splat.cpp:262
   const std::string out = arg(argc, argv, "--out", "");
   const int device = std::atoi(arg(argc, argv, "--device", "0"));
-  if (input.empty() && !synthetic) {
+  const std::string cache = arg(argc, argv, "--cache", "");   // scene cache: read if present, else written after the PLY conversion
+  if (input.empty() && !synthetic && cache.empty()) {
     std::fprintf(stderr, "usage: %s --input scene.ply | --synthetic N  [--width W --height H --frames K --scale-div D "
-                         "--out frame.ppm --device I]\n", argv[0]);
+                         "--out frame.ppm --device I --cache scene.gsc]\n", argv[0]);
     return 2;
   }
   std::vector<splat::Gaussian3DRecord> g;
@@ -228,10 +262,13 @@ int main(int argc, char **argv) {
       hi = {std::max(hi.x, r.mean[0]), std::max(hi.y, r.mean[1]), std::max(hi.z, r.mean[2])};
     }
     bmin = lo; bmax = hi;
+  } else if (!cache.empty() && cache_read(cache, g, bmin, bmax)) {
+    std::fprintf(stderr, "scene cache %s: %zu Gaussians\n", cache.c_str(), g.size());
   } else {
     std::string err;
     if (!gaussians_from_ply(input, g, err)) { std::fprintf(stderr, "%s: %s\n", input.c_str(), err.c_str()); return 2; }
     recentre_negate_z(g, bmin, bmax);
+    if (!cache.empty() && !cache_write(cache, g, bmin, bmax)) std::fprintf(stderr, "cannot write scene cache %s\n", cache.c_str());
   }
   const float fov = 40.0f * 0.017453292519943295f;   // glm::radians(40.f), splat.cpp:170
   const Mat4 proj = app_projection(bmin, bmax, fov, (float)W / (float)H);

@@ -247,3 +247,33 @@ def multiview_cameras(g16: np.ndarray, n_orbit: int = 32, n_spiral: int = 32) ->
         eye = centre + r * np.array([np.cos(ang), F32(0.35) * np.sin(F32(0.5) * ang), np.sin(ang)], dtype=F32)
         views.append(look_at(eye.astype(F32), centre, (0.0, 1.0, 0.0)))
     return views
+
+
+# ---- scene cache (same file as apps/splat_b200.cpp --cache) -----------------------
+CACHE_MAGIC = b"GSPLB200"
+
+
+def save_scene_cache(path: str, g16: np.ndarray) -> None:
+    """The converted scene (16-float records after the PLY conversion and recentre + z-negate) as one
+    flat little-endian file: magic | u32 version (1) | u32 0 | u64 n | f32 bbox min[3], max[3] | records."""
+    g = np.ascontiguousarray(g16, dtype="<f4").reshape(-1, 16)
+    bmin, bmax = bounds(g[:, 0:3]) if len(g) else (np.zeros(3, F32), np.zeros(3, F32))
+    with open(path, "wb") as fh:
+        fh.write(CACHE_MAGIC)
+        fh.write(np.array([1, 0], dtype="<u4").tobytes())
+        fh.write(np.array([len(g)], dtype="<u8").tobytes())
+        fh.write(np.concatenate([bmin, bmax]).astype("<f4").tobytes())
+        fh.write(g.tobytes())
+
+
+def load_scene_cache(path: str) -> np.ndarray:
+    """Records written by save_scene_cache / the C++ driver; raises ValueError on a foreign file."""
+    with open(path, "rb") as fh:
+        head = fh.read(48)
+        if len(head) != 48 or head[:8] != CACHE_MAGIC or int(np.frombuffer(head, "<u4", 1, 8)[0]) != 1:
+            raise ValueError(f"{path}: not a gsplat-b200 scene cache")
+        n = int(np.frombuffer(head, "<u8", 1, 16)[0])
+        g = np.fromfile(fh, dtype="<f4", count=n * 16)
+    if g.size != n * 16:
+        raise ValueError(f"{path}: truncated scene cache")
+    return g.reshape(n, 16).astype(F32, copy=False)

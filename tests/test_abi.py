@@ -154,3 +154,24 @@ def test_cpp_host_driver_builds_and_fails_loudly_without_a_device():
     else:
         assert r.returncode == 3 and r.stdout.startswith("no-device:"), r.stdout + r.stderr
     assert subprocess.run([os.path.join(root, "apps", "splat_b200")], capture_output=True).returncode == 2   # usage
+
+
+def test_scene_cache_round_trip(tmp_path):
+    """the converted scene as a flat file (shared with apps/splat_b200 --cache)."""
+    from gaussian_splat_ipu_b200 import scene as sc
+    from gaussian_splat_ipu_b200.splatter import synth_scene
+    g = synth_scene(777, 9)
+    p = str(tmp_path / "scene.gsc")
+    sc.save_scene_cache(p, g)
+    assert os.path.getsize(p) == 48 + g.size * 4
+    h = sc.load_scene_cache(p)
+    assert h.dtype == np.float32 and np.array_equal(h.view(np.uint32), g.view(np.uint32))
+    with open(p, "r+b") as fh:
+        fh.write(b"NOTACACHE")
+    with pytest.raises(ValueError):
+        sc.load_scene_cache(p)
+    sc.save_scene_cache(p, g)
+    with open(p, "r+b") as fh:
+        fh.truncate(48 + 100)
+    with pytest.raises(ValueError):
+        sc.load_scene_cache(p)
