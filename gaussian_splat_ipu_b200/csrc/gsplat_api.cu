@@ -91,6 +91,16 @@ struct gsplat_ctx {
   // the frames round-robin; result reads go to the lane of the frame rendered last.
   std::vector<gsplat_ctx *> lanes;
   int next_lane = 0, last_lane = 0;
+  // Slicing mode under a dispatcher.  A lane cannot tune itself: with other frames in flight its
+  // frame times measure the neighbours' load.  The dispatcher decides for all lanes from frames it
+  // runs ALONE: every DISPATCH_AUTO_PERIOD frames it drains the lanes and renders one frame in each
+  // mode by itself (the caller's own frames, in order), then keeps the faster mode (3 % hysteresis).
+  int forced_mode = -1;             // lane: -1 = decide locally, 0 = one slice, 1 = sliced
+  int d_mode = 1, d_phase = 0;      // dispatcher: mode in use; measured frames still to run
+  int d_retries = 0;                // measurements repeated because the frame overflowed
+  uint64_t d_frames = 0;
+  double d_ms[2] = {0.0, 0.0};
+  cudaEvent_t d_t0 = nullptr, d_t1 = nullptr;
   SortBuffers sort_a{}, sort_b{};
   int sorted_a = 0, sorted = 0;    // which of sort_x.keys/vals holds the sorted result
   unsigned long long *lookback = nullptr;
@@ -112,6 +122,7 @@ struct gsplat_ctx {
   uint64_t nsamples[2] = {0, 0};
   bool ema_valid[2] = {false, false};
   uint64_t auto_frames = 0, mode_frames[2] = {0, 0};
+  int auto_mode = -1;               // the mode the auto-tuner currently renders with (-1: none yet)
   SliceFractions slice_fr{};       // cumulative fractions of the thresholds (num_slices - 1 of them)
   unsigned long long *sel_lookback = nullptr;   // selection chains, one per slice
   // Everything that is zeroed at the start of every frame sits in two blocks so that a frame starts
@@ -238,6 +249,7 @@ void plan_slices(gsplat_ctx *ctx) {
   ctx->ema_valid[0] = ctx->ema_valid[1] = false;
   ctx->nsamples[0] = ctx->nsamples[1] = 0;
   ctx->auto_frames = 0;
+  ctx->auto_mode = -1;
   ctx->slice_fr.count = want - 1;
   for (int s = 0; s + 1 < want; ++s) ctx->slice_fr.f[s] = (float)frac[s];
 }
@@ -294,6 +306,8 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   if (!ctx) return;
   if (!ctx->lanes.empty()) {
     for (gsplat_ctx *lane : ctx->lanes) gsplat_destroy(lane);
+    if (ctx->d_t0) cudaEventDestroy(ctx->d_t0);
+    if (ctx->d_t1) cudaEventDestroy(ctx->d_t1);
     delete ctx;
     return;
   }
@@ -384,6 +398,11 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
           return rc;
         }
         outer->lanes.push_back(lane);
+      }
+      cudaSetDevice(cfg->device);
+      if (cudaEventCreate(&outer->d_t0) != cudaSuccess || cudaEventCreate(&outer->d_t1) != cudaSuccess) {
+        gsplat_destroy(outer);
+        return fail(nullptr, GSPLAT_E_CUDA, "gsplat_create: cudaEventCreate failed");
       }
       *out = outer;
       return GSPLAT_OK;

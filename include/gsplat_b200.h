@@ -67,7 +67,8 @@ typedef struct gsplat_config {
                          /* chain of short, latency-bound launches, so consecutive frames run on    */
                          /* separate streams with their own working buffers ("lanes", round-robin)  */
                          /* and interleave on the SMs.  Every call that reads a result refers to    */
-                         /* the frame rendered last.  0 = default: GSPLAT_DEFAULT_CONCURRENT_FRAMES, */
+                         /* the frame rendered last; the depth_slices = 0 choice is then made for   */
+                         /* all lanes from frames run alone.  0 = default: GSPLAT_DEFAULT_CONCURRENT_FRAMES, */
                          /* or 1 when collect_timings / debug_records are set.  Costs one set of    */
                          /* buffers (about 250 bytes per Gaussian) per frame in flight.             */
 } gsplat_config;
