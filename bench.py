@@ -186,7 +186,8 @@ def reference_arm(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "gaussians": n, "width": W, "height": H, "tile": "32x20",
-                       "scale_div": SCALE_DIV, "views": "orbit"}, "steps_timed": steps,
+                       "scale_div": SCALE_DIV, "views": f"orbit of {ORBIT_VIEWS}, one view per step (same cameras as "
+                                                         f"the b200 arm's rank 0)"}, "steps_timed": steps,
             "mgaussians_per_s": n * fps / 1e6,
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
                              "sample": f"{steps} full frames of {args.workload} (of {args.steps} requested steps; "
