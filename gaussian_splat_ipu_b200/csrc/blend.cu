@@ -41,7 +41,10 @@ __device__ __forceinline__ float ex2_approx(float x) {
 //   sA float4: mean.x, mean.y, -0.5*log2e*A, -log2e*B     sB float4: -0.5*log2e*C, opacity, r, g
 //   sC float2: b, conservative log2 threshold (skip when power2 < it)
 //   sRows u16: row_lo | row_hi << 5 | mask of the part's 8-pixel column blocks << 10 ; 1: touches nothing
-constexpr uint32_t BLEND_BATCH = 2;   // list entries staged per thread and batch
+#ifndef GSPLAT_BLEND_BATCH
+#define GSPLAT_BLEND_BATCH 2
+#endif
+constexpr uint32_t BLEND_BATCH = GSPLAT_BLEND_BATCH;   // list entries staged per thread and batch
 constexpr size_t BLEND_SMEM_PER_THREAD = BLEND_BATCH * (16 + 16 + 8 + 2);
 
 //
