@@ -595,6 +595,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stage-report", default=None, help="write the per-stage roofline table (JSON) to this path")
     args = ap.parse_args()
+    # stdout carries the ONE JSON line and nothing else: libraries that write to file descriptor 1
+    # themselves (NCCL prints "NCCL version ..." there at init under torchrun) are sent to stderr;
+    # Python's own stdout keeps the original descriptor.
+    sys.stdout.flush()
+    sys.stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         reference_arm(args)
     elif args.mode == "bands":
