@@ -28,33 +28,80 @@ sys.path.insert(0, ROOT)
 from gaussian_splat_ipu_b200 import scene as sc  # noqa: E402
 
 WORKLOADS = {
-    # name: (N gaussians, W, H, seed, description)
+    # synthetic: (N gaussians, W, H, seed, description)
     "synthetic-6M-1080p": (6_000_000, 1920, 1080, 0xB2000006, "north-star target: 6M synthetic Gaussians at 1920x1080"),
     "synthetic-1M-1080p": (1_000_000, 1920, 1080, 0xB2000003, "BASELINE configs[2]: 1M synthetic Gaussians at 1920x1080"),
     "synthetic-6M-4k": (6_000_000, 3840, 2160, 0xB2000004, "BASELINE configs[3]: 6M synthetic Gaussians at 3840x2160"),
     "synthetic-3M-1080p": (3_000_000, 1920, 1080, 0xB2000005, "BASELINE configs[4] scene: 3M synthetic Gaussians at 1920x1080"),
     "synthetic-200k-720p": (200_000, 1280, 720, 0xB2000001, "small functional check"),
 }
+# shipped PLY scenes (BASELINE configs[0] and [1]); data/bonsai-7k-mini.ply and point_cloud_8.ply are
+# missing from the reference mount (.MISSING_LARGE_BLOBS): config 0 runs on point_cloud_9 (the largest
+# shipped), config 1 on point_cloud_9..12.  Both scale divisors of SURVEY §8d: 0.1 (as shipped) and 1.0.
+PLY_WORKLOADS = {
+    "ply-point_cloud_9-720p-div0.1": (["point_cloud_9.ply"], 0.1, "fixed", "BASELINE configs[0] (bonsai absent: point_cloud_9), mvpStart camera, scale divisor as shipped"),
+    "ply-point_cloud_9-720p-div1.0": (["point_cloud_9.ply"], 1.0, "fixed", "BASELINE configs[0] (bonsai absent: point_cloud_9), mvpStart camera, true PLY scales"),
+    "ply-orbit-720p-div0.1": (["point_cloud_9.ply", "point_cloud_10.ply", "point_cloud_11.ply", "point_cloud_12.ply"], 0.1, "orbit",
+                              "BASELINE configs[1]: point_cloud_9..12 (8 absent), 32-frame mvpStart orbit, scale divisor as shipped"),
+    "ply-orbit-720p-div1.0": (["point_cloud_9.ply", "point_cloud_10.ply", "point_cloud_11.ply", "point_cloud_12.ply"], 1.0, "orbit",
+                              "BASELINE configs[1]: point_cloud_9..12 (8 absent), 32-frame mvpStart orbit, true PLY scales"),
+}
 DEFAULT_WORKLOAD = "synthetic-6M-1080p"
 ORBIT_VIEWS = 64
+PLY_ORBIT_VIEWS = 32
 FOV = sc.DEFAULT_FOV
-SCALE_DIV = 1.0
 PREWARM_FRAMES = 30    # extra untimed frames before the W warm-up steps of the GPU arm
 REF_BUDGET_S = 120.0   # wall-clock bound on the timed frames of the CPU reference arm
+# scene INPUT files (data, not code) shipped beside the compiled reference by oracle/build_ref.sh
+SCENE_DATA = os.path.join(ROOT, "oracle", "_ref", "data")
 
 
-def make_scene(name):
-    from gaussian_splat_ipu_b200.splatter import synth_scene
+class Scene:
+    """One workload: records, cameras (one per step, cyclic), projection, geometry."""
+
+    def __init__(self, name, g, views, proj, W, H, scale_div, views_note, l2_note, data):
+        self.name, self.g, self.views, self.proj, self.W, self.H = name, g, views, proj, W, H
+        self.scale_div, self.views_note, self.l2_note, self.data = scale_div, views_note, l2_note, data
+        self.small = g.shape[0] * 116 < 126e6      # scene + records fit the 126 MB L2
+
+    def config(self):
+        """The `config` object of the JSON line: identical for the b200 and the reference arm."""
+        return {"workload": self.name, "gaussians": int(self.g.shape[0]), "width": self.W, "height": self.H, "tile": "32x20",
+                "scale_div": self.scale_div, "views": self.views_note, "l2": self.l2_note}
+
+
+def load_ply_scene(fname):
+    p = os.path.join(SCENE_DATA, fname)
+    if not os.path.exists(p):
+        raise FileNotFoundError(f"{p}: PLY scenes are copied there by oracle/build_ref.sh (python __graft_entry__.py)")
+    return sc.gaussians_from_ply(sc.load_ply(p))
+
+
+def make_scene(name, ply_index=0):
+    if name in PLY_WORKLOADS:
+        files, div, cam, _ = PLY_WORKLOADS[name]
+        g = load_ply_scene(files[ply_index])
+        W, H = 1280, 720
+        proj = sc.app_projection(g, FOV, W, H)
+        if cam == "fixed":
+            views, note = [sc.mvp_start()], "one fixed camera: mvpStart (src/main/splat.cpp:235-241)"
+        else:
+            views = [sc.orbit_view(k, PLY_ORBIT_VIEWS) for k in range(PLY_ORBIT_VIEWS)]
+            note = f"{PLY_ORBIT_VIEWS}-frame orbit glm::rotate(mvpStart, 11.25 deg * k, y), each of {len(files)} PLYs in turn"
+        l2 = "scene smaller than L2 by nature (<= 44k Gaussians): L2 flushed (256 MB device write) between timed frames"
+        return Scene(name, g, views, proj, W, H, div, note, l2, "shipped PLY scene(s)")
     n, W, H, seed, _ = WORKLOADS[name]
-    g = synth_scene(n, seed)
+    g = sc.synth_scene(n, seed)      # host-only generator library: neither arm needs the product library for it
     bb = sc.bounds(g[:, 0:3])
     base = sc.look_at_bounding_box(bb, (0.0, 1.0, 1.0), 1.0)
     proj = sc.app_projection(g, FOV, W, H)
-    return g, base, proj, W, H
-
-
-def view_for(base, k):
-    return sc.rotate(base, np.radians(np.float32(360.0 / ORBIT_VIEWS * (k % ORBIT_VIEWS))), (0.0, 1.0, 0.0))
+    views = [sc.rotate(base, np.radians(np.float32(360.0 / ORBIT_VIEWS * k)), (0.0, 1.0, 0.0)) for k in range(ORBIT_VIEWS)]
+    l2 = "inputs larger than L2 (scene + records > 126 MB) and a new camera every step"
+    sn = Scene(name, g, views, proj, W, H, 1.0, f"orbit of {ORBIT_VIEWS}, one view per GPU per step (rank r renders view step*N + r)", l2,
+               "synthetic")
+    if sn.small:
+        sn.l2_note = "scene smaller than L2: L2 flushed (256 MB device write) between timed frames"
+    return sn
 
 
 class ClockSampler(threading.Thread):
@@ -128,19 +175,24 @@ def measured_peaks():
 
 
 def frame_traffic():
-    """Per-stage DRAM bytes of one frame from the newest committed ncu capture
-    (profiles/traffic_r*.json, written by profiles/traffic_frame.py); {} if there is none."""
+    """Per-stage DRAM bytes of one frame from the newest committed ncu capture: the
+    profiles/traffic_r*.json (written by profiles/traffic_frame.py) whose NAME sorts last (round,
+    then letter: r1 < r1d < r1f < r2 < r2a ...); {} if there is none."""
     import glob
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "traffic_r*.json")), key=os.path.getmtime)
-    for f in reversed(files):
+    import re
+
+    def key(f):
+        m = re.search(r"traffic_r(\d+)([a-z]*)\.json$", os.path.basename(f))
+        return (int(m.group(1)), m.group(2)) if m else (-1, "")
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "traffic_r*.json")), key=key, reverse=True):
         try:
             with open(f) as fh:
                 d = json.load(fh)
             if "stages" in d:
-                return {k: v["dram_bytes"] for k, v in d["stages"].items()}, os.path.basename(f)
+                return {k: v["dram_bytes"] for k, v in d["stages"].items()}, os.path.basename(f), d.get("pipes", {})
         except Exception:
             pass
-    return {}, None
+    return {}, None, {}
 
 
 def host_threads():
@@ -152,13 +204,64 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def cpu_frame_time(kind, g, view, proj, W, H, threads=0):
+def cpu_frame_time(kind, scn, view, threads=0):
     from oracle import pyoracle
     orc = pyoracle.Oracle(kind)
     threads = threads or host_threads()
     t0 = time.perf_counter()
-    f = orc.frame(g, view, proj, FOV, SCALE_DIV, W, H, render=True, threads=threads)
+    f = orc.frame(scn.g, view, scn.proj, FOV, scn.scale_div, scn.W, scn.H, render=True, threads=threads)
     return time.perf_counter() - t0, threads, f
+
+
+def cpu_extras(kind, scn, view):
+    """BASELINE.md §3's other CPU figures, for the shipped PLY scenes: the converged-frame code on ONE
+    thread, and (when the reference's own code is compiled here) O1 "as shipped": the unmodified GSplat
+    vertices over the 4-neighbour lattice with the shipped capacities (600 spare slots per tile, 75
+    Gaussians per channel: src/splat/ipu_rasteriser.cpp:307-316, src/splat/edge_builder.cpp:35-84),
+    steady state after 60 program runs."""
+    from oracle import pyoracle
+    out = {}
+    dt1, _, _ = cpu_frame_time(kind, scn, view, threads=1)
+    out["o2_one_thread"] = {"value": 1.0 / dt1, "unit": "frames/s", "cores": 1, "sample": f"1 frame, {dt1:.2f} s"}
+    if kind == "reference":
+        orc = pyoracle.Oracle("reference")
+        dt, copies = orc.lattice_time(scn.g, view, scn.proj, FOV, scn.scale_div, scn.W, scn.H, warm=60, timed=3,
+                                      threads=host_threads())
+        out["o1_as_shipped"] = {"value": 1.0 / dt, "unit": "frames/s", "cores": host_threads(),
+                                "sample": f"3 program runs after 60 warm-up runs, {dt * 1e3:.0f} ms each; lossy: {copies} copies "
+                                          f"rendered (the fixed buffers overflow, BASELINE.md)"}
+    return out
+
+
+def parity_of(scn, view, f):
+    """The GPU frame of `view` in the configuration the bench times (depth slices) against the CPU
+    reference frame `f` of the same view: framebuffer error, counts, and every tile's list an exact
+    prefix of the reference's list (complete lists when the library renders the scene in one slice)."""
+    from oracle import pyoracle
+    from gaussian_splat_ipu_b200.splatter import B200Splatter
+    sliced = scn.g.shape[0] >= 65536
+    p = B200Splatter(scn.g, scn.W, scn.H, debug_records=True, depth_slices=2 if sliced else 1)
+    p.updateProjection(scn.proj); p.updateFocalLengths(FOV, scn.scale_div); p.updateModelView(view)
+    p.execute(sync=True)
+    fb = p.framebuffer_tiled()
+    counts = p.getIPUHistogram()
+    off, lst = p.tile_lists()
+    st = p.stats()
+    p.close()
+    lens, full = np.diff(off), np.diff(f.offsets)
+    ok_len = bool((lens <= full).all())
+    prefixes = False
+    if ok_len:
+        tile_of = np.repeat(np.arange(lens.size), lens)
+        pos = np.arange(lst.size) - np.repeat(off[:-1], lens)
+        prefixes = bool(np.array_equal(lst, f.lists[f.offsets[tile_of] + pos]))
+    d = np.abs(fb.astype(np.float64) - f.fb.astype(np.float64))
+    return {"fb_max_abs": float(d.max()), "psnr_db": float(pyoracle.psnr(fb, f.fb)), "tolerance": "1/255 per channel, PSNR >= 50 dB",
+            "counts_equal": bool(np.array_equal(counts, np.diff(f.offsets).astype(np.uint32))),
+            "lists_are_prefixes": prefixes, "lists_complete": bool(ok_len and int(lens.sum()) == int(full.sum())),
+            "depth_slices": int(st.depth_slices), "pairs_binned": int(lens.sum()), "pairs_reference": int(full.sum()),
+            "pass": bool(d.max() <= 1.0 / 255.0 and pyoracle.psnr(fb, f.fb) >= 50.0 and prefixes
+                         and np.array_equal(counts, np.diff(f.offsets).astype(np.uint32)))}
 
 
 def reference_arm(args):
@@ -168,27 +271,31 @@ def reference_arm(args):
         return
     from oracle import pyoracle
     kind = "reference" if pyoracle.have_ref() else "port"
-    g, base, proj, W, H = make_scene(args.workload)
-    n = g.shape[0]
-    # bounded sample: one step = one full frame of the same scene/camera orbit on ALL host threads;
-    # a CPU frame takes seconds, so at most REF_BUDGET_S seconds of timed frames are run (>= 2) and
-    # the line says how many of the requested steps that was
-    times = []
-    cores = 0
-    dt, cores, _ = cpu_frame_time(kind, g, view_for(base, 0), proj, W, H)          # warm-up (1 frame)
-    steps = max(2, min(args.steps, int(REF_BUDGET_S / max(dt, 1e-3))))
-    for k in range(steps):
-        dt, cores, _ = cpu_frame_time(kind, g, view_for(base, args.warmup + k), proj, W, H)
-        times.append(dt)
+    nply = len(PLY_WORKLOADS[args.workload][0]) if args.workload in PLY_WORKLOADS else 1
+    times, cores, n_total, cfg = [], 0, 0, None
+    steps_req = args.steps
+    for pi in range(nply):
+        scn = make_scene(args.workload, pi)
+        cfg = cfg or scn.config()
+        n_total += scn.g.shape[0]
+        # bounded sample: one step = one full frame of the same scene/camera sequence on ALL host
+        # threads; a CPU frame takes up to seconds, so at most REF_BUDGET_S seconds of timed frames are
+        # run (>= 2 per scene) and the line says how many of the requested steps that was
+        dt, cores, _ = cpu_frame_time(kind, scn, scn.views[0])          # warm-up (1 frame)
+        steps = max(2, min(steps_req, int(REF_BUDGET_S / nply / max(dt, 1e-3))))
+        for k in range(steps):
+            dt, cores, _ = cpu_frame_time(kind, scn, scn.views[(args.warmup + k) % len(scn.views)])
+            times.append(dt)
+    if nply > 1:
+        cfg["gaussians"] = n_total
     total = float(np.sum(times))
+    steps = len(times)
     fps = steps / total
     line = {"impl": "reference", "metric": "frames_per_second", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "gaussians": n, "width": W, "height": H, "tile": "32x20",
-                       "scale_div": SCALE_DIV, "views": f"orbit of {ORBIT_VIEWS}, one view per step (same cameras as "
-                                                         f"the b200 arm's rank 0)"}, "steps_timed": steps,
-            "mgaussians_per_s": n * fps / 1e6,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": scn.data,
+            "config": cfg, "steps_timed": steps,
+            "mgaussians_per_s": n_total / nply * fps / 1e6,
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
                              "sample": f"{steps} full frames of {args.workload} (of {args.steps} requested steps; "
                                        f"{REF_BUDGET_S:.0f} s bound), all host threads (OpenMP)"},
@@ -254,18 +361,20 @@ def gpu_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    g, base, proj, W, H = make_scene(args.workload)
+    nply = len(PLY_WORKLOADS[args.workload][0]) if args.workload in PLY_WORKLOADS else 1
+    if nply > 1:
+        return ply_orbit_arm(args)
+    scn = make_scene(args.workload)
+    g, proj, W, H, views = scn.g, scn.proj, scn.W, scn.H, scn.views
     n = g.shape[0]
     s = B200Splatter(g, W, H, device=local)     # production configuration: frame graphs, no stage events
     s.updateProjection(proj)
-    s.updateFocalLengths(FOV, SCALE_DIV)
+    s.updateFocalLengths(FOV, scn.scale_div)
 
-    # camera matrices are host inputs: build the orbit once so the timed loops measure the render
+    # camera matrices are host inputs, built once (make_scene) so the timed loops measure the render
     # path, not numpy
-    views = [view_for(base, k) for k in range(ORBIT_VIEWS)]
-
     def step(k):
-        s.updateModelView(views[(k * world + rank) % ORBIT_VIEWS])
+        s.updateModelView(views[(k * world + rank) % len(views)])
         s.execute()
 
     K, Wm = args.steps, args.warmup
@@ -282,11 +391,21 @@ def gpu_arm(args):
     sampler.arm()
     l0 = launch_count()
     t0 = time.perf_counter()
-    s.timer_begin()
-    for k in range(K):
-        step(Wm + k)
-    dev_ms = s.timer_end()          # waits for the last frame
-    wall = time.perf_counter() - t0
+    if scn.small:
+        # the scene fits L2: flush it between frames and time every frame on the device by itself
+        dev_ms = 0.0
+        for k in range(K):
+            s.flush_l2()
+            s.timer_begin()
+            step(Wm + k)
+            dev_ms += s.timer_end()
+        wall = dev_ms * 1e-3
+    else:
+        s.timer_begin()
+        for k in range(K):
+            step(Wm + k)
+        dev_ms = s.timer_end()          # waits for the last frame
+        wall = time.perf_counter() - t0
     launches = launch_count() - l0
     barrier()
     clocks = sampler.finish()
@@ -297,7 +416,7 @@ def gpu_arm(args):
 
     # ---- end-to-end legs: host camera in, BGR8 frame + tile counts out to pinned host memory ----
     def set_view(k):
-        s.updateModelView(views[(k * world + rank) % ORBIT_VIEWS])
+        s.updateModelView(views[(k * world + rank) % len(views)])
 
     # (a) strictly sequential calls, as the reference's loop makes them: execute, getFrameBuffer,
     #     getIPUHistogram (src/main/splat.cpp:263-266,222)
@@ -350,15 +469,15 @@ def gpu_arm(args):
     # same slicing as the production run settled on (its last frames), fixed so every timed frame is alike
     sliced = st.depth_slices > 1 or st.num_duplicates < 0.6 * st.num_reference_duplicates
     ss = B200Splatter(g, W, H, device=local, collect_timings=True, depth_slices=2 if sliced else 1)
-    ss.updateProjection(proj); ss.updateFocalLengths(FOV, SCALE_DIV)
+    ss.updateProjection(proj); ss.updateFocalLengths(FOV, scn.scale_div)
     for k in range(PREWARM_FRAMES):
-        ss.updateModelView(views[k % ORBIT_VIEWS]); ss.execute()
+        ss.updateModelView(views[k % len(views)]); ss.execute()
     ss.sync()
     ss.timings_accum(reset=True)
     for k in range(min(K, 100)):
-        ss.updateModelView(views[((Wm + k) * world + rank) % ORBIT_VIEWS]); ss.execute()
+        ss.updateModelView(views[((Wm + k) * world + rank) % len(views)]); ss.execute()
     tm, nframes = ss.timings_accum(reset=True)
-    ss.updateModelView(views[(Wm * world + rank) % ORBIT_VIEWS]); ss.execute(); ss.sync()
+    ss.updateModelView(views[(Wm * world + rank) % len(views)]); ss.execute(); ss.sync()
     pairs, blended = ss.count_pairs()
     st = ss.stats()
     ss.close()
@@ -368,43 +487,57 @@ def gpu_arm(args):
     single = [k for k in ("k1_project", "k2_duplicate", "k4_ranges", "k5_blend") if k in stages]
     dom = max(single or stages, key=lambda k: stages[k]["ms"])
     r = stages[dom]
-    traffic, traffic_src = frame_traffic()
+    traffic, traffic_src, pipes = frame_traffic()
     roofline = {"kernel": dom, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
                 "frac": r["frac"], "traffic": traffic.get(dom), "traffic_unit": "DRAM bytes per frame, all launches of the stage",
-                "traffic_source": traffic_src, "algorithmic_bytes": r.get("alg_bytes"), "peak_source": peak_src, "ms": r["ms"]}
+                "traffic_source": traffic_src, "algorithmic_bytes": r.get("alg_bytes"),
+                "peak_source": (f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)" if r["bound"] == "hbm" else
+                                "computed 2*128*148*f_SM at the SM clock sampled during the timed region "
+                                "(MEASURED_PEAKS.json has no FP32 entry)"),
+                "ms": r["ms"]}
+    if pipes.get(dom):      # hardware-side view of the same kernel from the committed ncu capture
+        roofline["ncu"] = pipes[dom]
     # the same frames with ONE depth slice (every tile's list complete, as the reference builds them):
     # reported beside the headline so the effect of the slices is visible; a bounded number of steps
     s1 = B200Splatter(g, W, H, device=local, depth_slices=1)
-    s1.updateProjection(proj); s1.updateFocalLengths(FOV, SCALE_DIV)
+    s1.updateProjection(proj); s1.updateFocalLengths(FOV, scn.scale_div)
     K1 = min(K, 90)
     for k in range(5 * s1.concurrent_frames):    # every lane has captured its frame graph
-        s1.updateModelView(views[k % ORBIT_VIEWS]); s1.execute()
+        s1.updateModelView(views[k % len(views)]); s1.execute()
     s1.sync()
     s1.timer_begin()
     for k in range(K1):
-        s1.updateModelView(views[((Wm + k) * world + rank) % ORBIT_VIEWS]); s1.execute()
+        s1.updateModelView(views[((Wm + k) * world + rank) % len(views)]); s1.execute()
     one_ms = s1.timer_end()
     st1 = s1.stats()
     one_slice = {"value": K1 / (one_ms * 1e-3), "unit": "frames/s per GPU", "steps": K1,
                  "duplicates": int(st1.num_duplicates), "depth_sorted": int(st1.num_depth_sorted),
-                 "note": "depth_slices=1: complete per-tile lists (bit-exact to the reference's), same framebuffer"}
+                 "note": "depth_slices=1: complete per-tile lists (bit-exact to the reference's), same framebuffer"
+                         + ("; L2 not flushed in this leg" if scn.small else "")}
     s1.close()
-    cpu = None
+    cpu, parity = None, None
     if args.gpus == 1 and not args.no_cpu_baseline:
         from oracle import pyoracle
         kind = "reference" if pyoracle.have_ref() else "port"
-        dt, cores, _ = cpu_frame_time(kind, g, view_for(base, Wm), proj, W, H)
+        view = views[Wm % len(views)]
+        dt, cores, f = cpu_frame_time(kind, scn, view)
         cpu = {"value": 1.0 / dt, "unit": "frames/s", "cores": cores, "kind": kind,
-               "sample": f"1 full frame of {args.workload} (view {Wm}), all host threads (OpenMP), {dt:.2f} s"}
+               "sample": f"1 full frame of {args.workload} (view {Wm % len(views)}), all host threads (OpenMP), {dt:.2f} s"}
+        # the frame just computed by the reference's CPU code is the parity reference for the GPU
+        # frame of the same view, in the configuration the headline is measured in
+        parity = parity_of(scn, view, f)
+        parity["reference"] = kind
+        if args.workload in PLY_WORKLOADS:
+            cpu.update(cpu_extras(kind, scn, view))
     line = {"metric": "frames_per_second", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": 1e3 * t_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "gaussians": n, "width": W, "height": H, "tile": "32x20",
-                       "scale_div": SCALE_DIV, "views": f"orbit of {ORBIT_VIEWS}, one view per GPU per step",
-                       "depth_slices": "library default (2): lists are exact prefixes of the reference's, "
-                                       "framebuffer and counts identical to the one-slice run",
-                       "concurrent_frames": depth // 2,
-                       "l2": "inputs larger than L2 (scene + records > 126 MB) and a new camera every step"},
+            "dtype": "f32", "data": scn.data,
+            "config": scn.config(),
+            "notes": {"depth_slices": "library default (2 on scenes >= 65536 Gaussians): lists are exact prefixes of the "
+                                      "reference's, framebuffer and counts identical to the one-slice run",
+                      "concurrent_frames": depth // 2,
+                      "timing": ("every frame timed alone on the device (cudaEvents), L2 flushed before it" if scn.small else
+                                 "K frames back to back, wall clock bracketed by synchronisation, max over ranks")},
             "mgaussians_per_s": n * fps / 1e6, "device_ms_per_step": dev_ms_max / K,
             "frame": {"drawn": int(st.num_drawn), "duplicates": int(st.num_duplicates),
                       "reference_duplicates": int(st.num_reference_duplicates),
@@ -413,7 +546,8 @@ def gpu_arm(args):
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": 34 * 4,
                     "d2h_bytes_per_step": W * H * 3 + s.num_tiles * 4 + 12,
                     "api": "executeStreamed/acquireFrame: three-slot frame stream per frame in flight, every frame "
-                           "delivered to pinned host memory inside the timed region",
+                           "delivered to pinned host memory inside the timed region"
+                           + (" (L2 not flushed in this leg)" if scn.small else ""),
                     "tickets_outstanding": depth,
                     "checksum": checksum_last, "same_frame_as_sequential": checksum_last == checksum_sync,
                     "sequential": {"value": sync_fps, "unit": "frames/s",
@@ -421,13 +555,95 @@ def gpu_arm(args):
                                    "d2h_bytes_per_step": W * H * 3 + s.num_tiles * 8 + 8}},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "stages": stages,
             "one_slice": one_slice,
-            "cpu_baseline": cpu}
+            "cpu_baseline": cpu, "parity": parity}
     if args.stage_report:
         with open(args.stage_report, "w") as fh:
             json.dump(line, fh, indent=1)
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def ply_orbit_arm(args):
+    """BASELINE configs[1] / SURVEY §8d config 2: each shipped PLY (point_cloud_9..12) rendered along the
+    32-frame mvpStart orbit at 1280x720; fps = frames / total device time.  One GPU.  Every frame is
+    compared with the CPU reference's frame of the same camera (the CPU frames are computed anyway for
+    the cpu_baseline figure): framebuffer, counts, complete lists."""
+    from gaussian_splat_ipu_b200.splatter import B200Splatter, launch_count
+    from oracle import pyoracle
+    _, _, local = dist_env()
+    files, div, _, _ = PLY_WORKLOADS[args.workload]
+    kind = "reference" if pyoracle.have_ref() else "port"
+    orc = None if args.no_cpu_baseline else pyoracle.Oracle(kind)
+    per_scene, tot_ms, tot_frames, tot_e2e_s, tot_cpu_s, launches = [], 0.0, 0, 0.0, 0.0, 0
+    worst = {"fb_max_abs": 0.0, "psnr_db": float("inf"), "counts_equal": True, "lists_equal": True, "frames": 0}
+    sampler = ClockSampler(local)
+    sampler.arm()
+    cfg = None
+    n_total = 0
+    for pi, fname in enumerate(files):
+        scn = make_scene(args.workload, pi)
+        cfg = cfg or scn.config()
+        n_total += scn.g.shape[0]
+        s = B200Splatter(scn.g, scn.W, scn.H, device=local, debug_records=False)
+        s.updateProjection(scn.proj); s.updateFocalLengths(FOV, scn.scale_div)
+        for v in scn.views[: max(args.warmup, 3)]:
+            s.updateModelView(v); s.execute()
+        s.sync()
+        l0 = launch_count()
+        ms = 0.0
+        for v in scn.views:                      # timed: each frame alone, cold L2
+            s.flush_l2()
+            s.updateModelView(v)
+            s.timer_begin(); s.execute(); ms += s.timer_end()
+        launches += launch_count() - l0
+        t0 = time.perf_counter()                 # e2e: the frame stream over the same orbit (L2 not flushed)
+        inflight = []
+        for v in scn.views:
+            s.updateModelView(v); inflight.append(s.executeStreamed())
+            if len(inflight) > 2 * s.concurrent_frames:
+                s.acquireFrame(inflight.pop(0))
+        for t in inflight:
+            s.acquireFrame(t)
+        e2e_s = time.perf_counter() - t0
+        s.close()
+        cpu_s = 0.0
+        if orc is not None:                      # CPU reference over the same orbit + parity of every frame
+            p = B200Splatter(scn.g, scn.W, scn.H, device=local, debug_records=True, depth_slices=1)
+            p.updateProjection(scn.proj); p.updateFocalLengths(FOV, scn.scale_div)
+            for v in scn.views:
+                t0 = time.perf_counter()
+                f = orc.frame(scn.g, v, scn.proj, FOV, scn.scale_div, scn.W, scn.H, render=True, threads=host_threads())
+                cpu_s += time.perf_counter() - t0
+                p.updateModelView(v); p.execute(sync=True)
+                fb = p.framebuffer_tiled()
+                off, lst = p.tile_lists()
+                worst["fb_max_abs"] = max(worst["fb_max_abs"], float(np.abs(fb - f.fb).max()))
+                worst["psnr_db"] = min(worst["psnr_db"], float(pyoracle.psnr(fb, f.fb)))
+                worst["counts_equal"] &= bool(np.array_equal(p.getIPUHistogram(), np.diff(f.offsets).astype(np.uint32)))
+                worst["lists_equal"] &= bool(np.array_equal(off, f.offsets) and np.array_equal(lst, f.lists))
+                worst["frames"] += 1
+            p.close()
+        nv = len(scn.views)
+        per_scene.append({"ply": fname, "gaussians": int(scn.g.shape[0]), "frames": nv, "fps": nv / (ms * 1e-3),
+                          "e2e_fps": nv / e2e_s, "cpu_fps": (nv / cpu_s) if cpu_s else None})
+        tot_ms += ms; tot_frames += nv; tot_e2e_s += e2e_s; tot_cpu_s += cpu_s
+    clocks = sampler.finish()
+    cfg["gaussians"] = n_total
+    fps = tot_frames / (tot_ms * 1e-3)
+    worst["pass"] = bool(worst["frames"] and worst["fb_max_abs"] <= 1 / 255 and worst["psnr_db"] >= 50 and
+                         worst["counts_equal"] and worst["lists_equal"])
+    line = {"metric": "frames_per_second", "value": fps, "unit": "frames/s", "n_gpus": 1, "steps": tot_frames,
+            "warmup": max(args.warmup, 3), "ms_per_step": tot_ms / tot_frames, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "shipped PLY scene(s)", "config": cfg, "scenes": per_scene,
+            "e2e": {"value": tot_frames / tot_e2e_s, "unit": "frames/s", "h2d_bytes_per_step": 136,
+                    "d2h_bytes_per_step": 1280 * 720 * 3 + 1440 * 4 + 12,
+                    "api": "executeStreamed/acquireFrame over each orbit (L2 not flushed in this leg)"},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "cpu_baseline": None if orc is None else {"value": tot_frames / tot_cpu_s, "unit": "frames/s", "cores": host_threads(),
+                                                      "kind": kind, "sample": f"all {tot_frames} frames, all host threads (OpenMP)"},
+            "parity": None if orc is None else dict(worst, reference=kind, tolerance="fb 1/255 per channel, PSNR >= 50 dB; lists bit-exact")}
+    print(json.dumps(line), flush=True)
 
 
 def bands_arm(args):
@@ -444,11 +660,11 @@ def bands_arm(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    g, base, proj, W, H = make_scene(args.workload)
+    scn = make_scene(args.workload)
+    g, proj, W, H, views = scn.g, scn.proj, scn.W, scn.H, scn.views
     s = B200Splatter(g, W, H, device=local, concurrent_frames=1)   # its device image is read in place
     s.updateProjection(proj)
-    s.updateFocalLengths(FOV, SCALE_DIV)
-    views = [view_for(base, k) for k in range(ORBIT_VIEWS)]
+    s.updateFocalLengths(FOV, scn.scale_div)
     bgr_ptr, _ = s.device_pointers()
     image = torch.as_tensor(sh.DeviceArray(bgr_ptr, (H * W * 3,), "|u1"), device=f"cuda:{local}")
     counts_dev = torch.zeros(s.num_tiles, dtype=torch.int32, device=f"cuda:{local}")
@@ -457,7 +673,7 @@ def bands_arm(args):
 
     def step(k):
         nonlocal cuts
-        s.updateModelView(views[k % ORBIT_VIEWS])
+        s.updateModelView(views[k % len(views)])
         s.set_band(cuts[rank], cuts[rank + 1])
         s.execute()
         s.postprocess_bgr8()
@@ -513,10 +729,11 @@ def multiview_arm(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    g, base, proj, W, H = make_scene(args.workload)
+    scn = make_scene(args.workload)
+    g, proj, W, H = scn.g, scn.proj, scn.W, scn.H
     s = B200Splatter(g, W, H, device=local)
     s.updateProjection(proj)
-    s.updateFocalLengths(FOV, SCALE_DIV)
+    s.updateFocalLengths(FOV, scn.scale_div)
     views = sc.multiview_cameras(g)
     nv = len(views)
 
@@ -588,7 +805,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + sorted(PLY_WORKLOADS))
     ap.add_argument("--mode", default="views", choices=["views", "bands", "multiview"],
                     help="views (default, the headline): one whole view per GPU per step; bands: one frame per "
                          "step split into tile-row bands over the GPUs, gathered to rank 0")

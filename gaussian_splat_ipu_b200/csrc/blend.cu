@@ -313,12 +313,6 @@ template <bool COUNT, bool FIRST, bool LAST>
 static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
                            float4 *fb_tiled, float *tstate, const TileState &ts, int split, const uint32_t *order,
                            unsigned long long *pair_counters, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(blend_kernel<COUNT, FIRST, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)(BLEND_MAX_ROWS * 32 * BLEND_SMEM_PER_THREAD));
-    attr_set = true;
-  }
   const int rows = fp.row_end - fp.row_begin;
   if (rows <= 0) return;
   const int full_h = (int)fp.tile_h;
@@ -329,6 +323,22 @@ static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, cons
   ++g_launches;
   blend_kernel<COUNT, FIRST, LAST><<<rows * fp.tiles_across * split, threads, smem, st>>>(
       p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, full_h, part_w, fb_tiled, tstate, ts, order, pair_counters);
+}
+
+template <bool COUNT, bool FIRST, bool LAST> static cudaError_t blend_attr() {
+  return cudaFuncSetAttribute(blend_kernel<COUNT, FIRST, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)(BLEND_MAX_ROWS * 32 * BLEND_SMEM_PER_THREAD));
+}
+// Dynamic shared memory opt-in of every K5 variant on the CURRENT device (the attribute belongs to
+// the device's context: gsplat_create runs this once per device).
+cudaError_t setup_blend_kernels() {
+  cudaError_t e = cudaSuccess;
+  auto acc = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+  acc(blend_attr<false, false, false>()); acc(blend_attr<false, false, true>());
+  acc(blend_attr<false, true, false>()); acc(blend_attr<false, true, true>());
+  acc(blend_attr<true, false, false>()); acc(blend_attr<true, false, true>());
+  acc(blend_attr<true, true, false>()); acc(blend_attr<true, true, true>());
+  return e;
 }
 
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,

@@ -207,12 +207,6 @@ void launch_duplicate(const Projected &p, const uint32_t *const sorted_gauss[2],
                       uint32_t capacity, unsigned long long *lookback, uint32_t *ticket, uint32_t *total,
                       uint32_t *overflow, cudaStream_t st) {
   if (!count_cap) return;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(duplicate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem));
-    cudaFuncSetAttribute(duplicate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem));
-    attr_set = true;
-  }
   ++g_launches;
   const int grid = ceil_div(count_cap, K2_CHUNK);
   if (tile_done)
@@ -311,13 +305,21 @@ live_sat_kernel(const uint8_t *__restrict__ tile_done, int tiles_across, int til
 }
 
 void launch_live_sat(const uint8_t *tile_done, int tiles_across, int tiles_down, uint32_t *sat, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(live_sat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_COUNT_MAX_SMEM);
-    attr_set = true;
-  }
   ++g_launches;
   live_sat_kernel<<<1, 1024, tile_count_smem(tiles_across, tiles_down), st>>>(tile_done, tiles_across, tiles_down, sat);
+}
+
+// Dynamic shared memory opt-in of K2 and the tile-grid kernels on the CURRENT device (per device:
+// gsplat_create runs this once for each).
+cudaError_t setup_duplicate_kernels() {
+  cudaError_t e = cudaSuccess;
+  auto acc = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+  acc(cudaFuncSetAttribute(duplicate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem)));
+  acc(cudaFuncSetAttribute(duplicate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem)));
+  acc(cudaFuncSetAttribute(live_sat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_COUNT_MAX_SMEM));
+  acc(cudaFuncSetAttribute(tile_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_COUNT_MAX_SMEM));
+  acc(cudaFuncSetAttribute(tile_count_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_COUNT_MAX_SMEM));
+  return e;
 }
 
 size_t tile_count_smem(int tiles_across, int tiles_down) {
@@ -327,12 +329,6 @@ size_t tile_count_smem(int tiles_across, int tiles_down) {
 void launch_tile_counts(const Projected &p, uint32_t n, int tiles_across, int tiles_down, int *diff, uint32_t *counts,
                         cudaStream_t st) {
   const size_t smem = tile_count_smem(tiles_across, tiles_down);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(tile_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_COUNT_MAX_SMEM);
-    cudaFuncSetAttribute(tile_count_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_COUNT_MAX_SMEM);
-    attr_set = true;
-  }
   g_launches += n ? 2 : 1;
   if (n) tile_count_kernel<<<148 * 2, TC_THREADS, smem, st>>>(p, n, tiles_across, tiles_down, diff);
   tile_count_finish_kernel<<<1, 1024, smem, st>>>(diff, tiles_across, tiles_down, counts);

@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -46,6 +47,9 @@ struct StreamSlot {
   cudaEvent_t rendered = nullptr, copied = nullptr;
   uint64_t ticket = 0, frame_no = 0;
   bool used = false;
+  // verdict of the frame this slot carries, latched when its FrameSlot resolves: the FrameSlot ring
+  // may be recycled (overflow re-runs consume extra slots) before the ticket is acquired
+  bool resolved = false, overflowed = false;
   FrameParams fp{};
 };
 
@@ -77,8 +81,9 @@ struct gsplat_ctx {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   std::string err;
   int tiles_across = 0, tiles_down = 0, num_tiles = 0, tile_bits = 0;
-  // scene
+  // scene (immutable after upload; the lanes of a dispatcher share lane 0's arrays: scene_owned = false)
   SceneSoA scene{};
+  bool scene_owned = true;
   // per-Gaussian frame buffers
   Projected proj{};
   float *dbg_rec8 = nullptr;
@@ -139,6 +144,7 @@ struct gsplat_ctx {
   // frame graphs: [0] one slice, [1] sliced; dropped whenever buffers, scene or band change
   FrameGraph graphs[2];
   bool use_graphs = true;          // GSPLAT_GRAPHS=0 disables (eager launches)
+  uint8_t *l2_scratch = nullptr;   // gsplat_flush_l2 (allocated on first use)
   float *tstate = nullptr;         // per pixel: transmittance carried between slices (-1 = stopped)
   unsigned long long *pair_counters = nullptr;   // non-null while a counting re-run is enqueued
   // parity tap: per-slice sorted lists of the last frame (filled only with cfg.debug_records)
@@ -214,6 +220,23 @@ int alloc_sort(gsplat_ctx *ctx, SortBuffers &s, size_t capacity) {
   return GSPLAT_OK;
 }
 
+// One-time kernel setup per DEVICE (not per process): the dynamic-shared-memory opt-in is stored in
+// the device's context, so a second context on another GPU of the same process needs its own.
+// Thread-safe: contexts may be created from several host threads (one per GPU).
+cudaError_t setup_device_kernels(int device) {
+  static std::mutex mu;
+  static bool done[256] = {false};
+  std::lock_guard<std::mutex> lock(mu);
+  if (device < 0 || device >= 256) return cudaErrorInvalidDevice;
+  if (done[device]) return cudaSuccess;
+  cudaError_t e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = setup_blend_kernels();
+  if (e == cudaSuccess) e = setup_duplicate_kernels();
+  if (e == cudaSuccess) e = setup_sort_kernels();
+  if (e == cudaSuccess) done[device] = true;
+  return e;
+}
+
 int ceil_log2(uint32_t v) { int b = 0; while ((1u << b) < v) ++b; return b; }
 
 // Depth slices: cumulative fractions of the drawn Gaussians (nearest first) at which the frame is
@@ -236,7 +259,9 @@ void plan_slices(gsplat_ctx *ctx) {
         char *end = nullptr;
         const double v = std::strtod(q, &end);
         if (end == q) break;
-        if (v > 0.0 && v < 1.0) frac[k++] = v;
+        // cut points must increase: a non-monotone list would make the slices' key intervals
+        // overlap and Gaussians would be binned and blended twice
+        if (v > 0.0 && v < 1.0 && (k == 0 || v > frac[k - 1])) frac[k++] = v;
         q = *end == ',' ? end + 1 : end;
       }
       want = k + 1;
@@ -297,6 +322,7 @@ int gsplat_config_default(gsplat_config *cfg) {
   cfg->width = 1280; cfg->height = 720;      // tile_config.hpp:5-6
   cfg->tile_w = 32; cfg->tile_h = 20;        // tile_config.hpp:9-15 (1280/40, 720/36)
   cfg->guard_factor = 15.0f;                 // codelets.cpp:622
+  cfg->band_row_end = -1;                    // all tile rows
   return GSPLAT_OK;
 }
 
@@ -305,7 +331,8 @@ const char *gsplat_last_error(const gsplat_ctx *ctx) { return ctx ? ctx->err.c_s
 void gsplat_destroy(gsplat_ctx *ctx) {
   if (!ctx) return;
   if (!ctx->lanes.empty()) {
-    for (gsplat_ctx *lane : ctx->lanes) gsplat_destroy(lane);
+    // lane 0 owns the scene arrays the others read: it goes last
+    for (size_t l = ctx->lanes.size(); l-- > 0;) gsplat_destroy(ctx->lanes[l]);
     if (ctx->d_t0) cudaEventDestroy(ctx->d_t0);
     if (ctx->d_t1) cudaEventDestroy(ctx->d_t1);
     delete ctx;
@@ -317,12 +344,13 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   cudaSetDevice(ctx->cfg.device);
   if (ctx->st) cudaStreamSynchronize(ctx->st);
   drop_graphs(ctx);
-  dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
+  if (ctx->scene_owned) { dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12); }
   dfree(ctx->proj.rec); dfree(ctx->proj.rect);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->frame_block); dfree(ctx->d_persist); dfree(ctx->chain_block);
   dfree(ctx->proj.depth_key);
   free_sort(ctx->sort_a); free_sort(ctx->sort_b);
   dfree(ctx->counts); dfree(ctx->fb); dfree(ctx->bgr);
+  dfree(ctx->l2_scratch);
   dfree(ctx->count_diff); dfree(ctx->live_sat); dfree(ctx->tile_order); dfree(ctx->tstate);
   if (ctx->copy_st) cudaStreamSynchronize(ctx->copy_st);
   for (auto &ss : ctx->sslots) {
@@ -413,7 +441,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   ctx->tiles_across = cfg->width / cfg->tile_w;
   ctx->tiles_down = cfg->height / cfg->tile_h;
   ctx->num_tiles = ctx->tiles_across * ctx->tiles_down;
-  if (ctx->cfg.band_row_begin == 0 && ctx->cfg.band_row_end == 0) ctx->cfg.band_row_end = ctx->tiles_down;
+  if (ctx->cfg.band_row_end < 0) ctx->cfg.band_row_end = ctx->tiles_down;   // -1: all rows ((0,0) is an EMPTY band)
   if (ctx->cfg.band_row_begin < 0 || ctx->cfg.band_row_end > ctx->tiles_down ||
       ctx->cfg.band_row_begin > ctx->cfg.band_row_end) {
     delete ctx;
@@ -429,6 +457,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     }                                                                                              \
   } while (0)
   CUC(cudaSetDevice(cfg->device));
+  CUC(setup_device_kernels(cfg->device));
   CUC(cudaStreamCreateWithFlags(&ctx->st, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&ctx->aux_st, cudaStreamNonBlocking));
   CUC(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
@@ -490,25 +519,34 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   return GSPLAT_OK;
 }
 
-int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
-  ROUTE_ALL(gsplat_upload_scene(ctx, g16, n));
-  if (!ctx || (!g16 && n)) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: null argument");
+// Scene upload of one (lane) context.  `shared` != nullptr: adopt another lane's device arrays
+// instead of uploading a copy (the scene is read-only after upload; only the per-frame working
+// buffers are per lane).
+static int upload_scene_impl(gsplat_ctx *ctx, const float *g16, size_t n, const SceneSoA *shared) {
+  if (!ctx || (!g16 && n && !shared)) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: null argument");
   if (n > 0x7fffffffull) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: too many Gaussians");
   CU(cudaSetDevice(ctx->cfg.device));
   CU(cudaStreamSynchronize(ctx->st));
   drop_graphs(ctx);
   for (auto &sl : ctx->slots) sl.pending = false;
-  dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12);
+  if (ctx->scene_owned) { dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12); }
+  ctx->scene = SceneSoA{};
+  ctx->scene_owned = true;
   dfree(ctx->proj.rec); dfree(ctx->proj.rect); dfree(ctx->chain_block);
   dfree(ctx->proj.depth_key);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4);
   ctx->have_scene = ctx->have_frame = false;
   const size_t na = n ? n : 1;
-  ctx->scene.n = (uint32_t)n;
-  CU(cudaMalloc(&ctx->scene.pos_s0, na * sizeof(float4)));
-  CU(cudaMalloc(&ctx->scene.quat, na * sizeof(float4)));
-  CU(cudaMalloc(&ctx->scene.rgba, na * sizeof(float4)));
-  CU(cudaMalloc(&ctx->scene.s12, na * sizeof(float2)));
+  if (shared) {
+    ctx->scene = *shared;
+    ctx->scene_owned = false;
+  } else {
+    ctx->scene.n = (uint32_t)n;
+    CU(cudaMalloc(&ctx->scene.pos_s0, na * sizeof(float4)));
+    CU(cudaMalloc(&ctx->scene.quat, na * sizeof(float4)));
+    CU(cudaMalloc(&ctx->scene.rgba, na * sizeof(float4)));
+    CU(cudaMalloc(&ctx->scene.s12, na * sizeof(float2)));
+  }
   CU(cudaMalloc(&ctx->proj.rec, na * 3 * sizeof(float4)));
   CU(cudaMemsetAsync(ctx->proj.rec, 0, na * 3 * sizeof(float4), ctx->st));
   CU(cudaMalloc(&ctx->proj.rect, na * sizeof(uint2)));
@@ -531,7 +569,7 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
     CU(cudaMemcpyAsync(ctx->d_persist + P_N, &n32, 4, cudaMemcpyHostToDevice, ctx->st));
     CU(cudaStreamSynchronize(ctx->st));
   }
-  if (n) {
+  if (n && !shared) {
     float *tmp = nullptr;
     CU(cudaMalloc(&tmp, n * 16 * sizeof(float)));
     cudaError_t e = cudaMemcpyAsync(tmp, g16, n * 16 * sizeof(float), cudaMemcpyHostToDevice, ctx->st);
@@ -549,6 +587,26 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
   }
   ctx->have_scene = true;
   return GSPLAT_OK;
+}
+
+int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
+  if (ctx && !ctx->lanes.empty()) {   // one upload; the other lanes adopt lane 0's read-only arrays
+    gsplat_ctx *first = ctx->lanes[0];
+    for (size_t l = 1; l < ctx->lanes.size(); ++l) {   // they may hold pointers into the arrays about to be freed
+      gsplat_ctx *lane = ctx->lanes[l];
+      cudaSetDevice(lane->cfg.device);
+      cudaStreamSynchronize(lane->st);
+      if (!lane->scene_owned) { lane->scene = SceneSoA{}; lane->scene_owned = true; lane->have_scene = false; }
+    }
+    int rc = upload_scene_impl(first, g16, n, nullptr);
+    if (rc < 0) { ctx->err = first->err; return rc; }
+    for (size_t l = 1; l < ctx->lanes.size(); ++l) {
+      rc = upload_scene_impl(ctx->lanes[l], nullptr, n, &first->scene);
+      if (rc < 0) { ctx->err = ctx->lanes[l]->err; return rc; }
+    }
+    return GSPLAT_OK;
+  }
+  return upload_scene_impl(ctx, g16, n, nullptr);
 }
 
 int gsplat_set_camera(gsplat_ctx *ctx, const float mv[16], const float proj[16], float fov, float scale_div) {
@@ -588,7 +646,8 @@ int gsplat_set_band(gsplat_ctx *ctx, int row_begin, int row_end) {
   ctx->cfg.band_row_end = row_end;
   ctx->fp.row_begin = row_begin;
   ctx->fp.row_end = row_end;
-  // tiles that leave the band must read count 0 (K5 only writes the counts of the tiles it renders)
+  // tiles that leave the band must read count 0 until the next frame's tile_count_finish_kernel
+  // rewrites every count (rectangles are clamped to the band in K1, so outside tiles count 0)
   CU(cudaSetDevice(ctx->cfg.device));
   CU(cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * ctx->num_tiles, ctx->st));
   return GSPLAT_OK;

@@ -242,6 +242,13 @@ void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *
 void launch_bgr8(const float4 *fb_tiled, uint8_t *bgr, int W, int H, int tile_w, int tile_h,
                  cudaStream_t st);
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of (kernel, device context): every
+// device a context is created on needs its own opt-in.  gsplat_create calls these once per device
+// (mutex-guarded table in gsplat_api.cu), with that device current.
+cudaError_t setup_blend_kernels();
+cudaError_t setup_duplicate_kernels();
+cudaError_t setup_sort_kernels();
+
 extern unsigned long long g_launches;   // kernels launched by this library (bench accounting)
 inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 

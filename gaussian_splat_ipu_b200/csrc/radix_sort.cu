@@ -331,14 +331,6 @@ void sort_plan(int nbits, int &passes, int &bits_per_pass, int max_bits) {
 template <int BITS>
 static void launch_pass(SortBuffers &sb, int cur, bool identity, const uint32_t *d_n, int shift, uint32_t grid,
                         const uint32_t *key_range, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(rs_scatter_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)rs_scatter_smem(BITS));
-    cudaFuncSetAttribute(rs_hist_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)rs_counter_words(BITS) * 4);
-    attr_set = true;
-  }
   rs_hist_kernel<BITS><<<grid, RS_THREADS, rs_counter_words(BITS) * 4, st>>>(sb.keys[cur], d_n, sb.capacity, shift,
                                                                             sb.block_hist, sb.max_tiles, key_range);
   rs_scan_kernel<<<1u << BITS, 256, 0, st>>>(sb.block_hist, sb.max_tiles, d_n, sb.capacity, sb.digit_totals, key_range,
@@ -346,6 +338,22 @@ static void launch_pass(SortBuffers &sb, int cur, bool identity, const uint32_t 
   rs_scatter_kernel<BITS><<<grid, RS_THREADS, rs_scatter_smem(BITS), st>>>(
       sb.keys[cur], identity ? nullptr : sb.vals[cur], sb.keys[cur ^ 1], sb.vals[cur ^ 1], d_n, sb.capacity, shift,
       sb.block_hist, sb.max_tiles, sb.digit_totals, key_range);
+}
+
+template <int BITS> static cudaError_t sort_attr() {
+  cudaError_t e = cudaFuncSetAttribute(rs_scatter_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)rs_scatter_smem(BITS));
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(rs_hist_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)rs_counter_words(BITS) * 4);
+}
+// Dynamic shared memory opt-in of every digit width on the CURRENT device (once per device).
+cudaError_t setup_sort_kernels() {
+  cudaError_t e = cudaSuccess;
+  auto acc = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+  acc(sort_attr<1>()); acc(sort_attr<2>()); acc(sort_attr<3>()); acc(sort_attr<4>());
+  acc(sort_attr<5>()); acc(sort_attr<6>()); acc(sort_attr<7>()); acc(sort_attr<8>());
+  return e;
 }
 
 int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, int begin_bit, int end_bit,

@@ -249,6 +249,28 @@ def multiview_cameras(g16: np.ndarray, n_orbit: int = 32, n_spiral: int = 32) ->
     return views
 
 
+# ---- synthetic scenes (SURVEY §8d generator) ----------------------------------------------------
+def synth_scene(n: int, seed: int) -> np.ndarray:
+    """Seeded synthetic scene as (n,16) Gaussian3D records, from the HOST-ONLY generator library
+    ``libgsplat_synth.so`` (csrc/synth.cpp compiled with g++, no CUDA).  Same stream of records as
+    ``gsplat_synth_scene`` of the product library; this entry exists so that callers that must not
+    map the product library (bench.py's CPU reference arm) can build the same scene."""
+    import ctypes as C
+    import os
+    here = os.path.dirname(os.path.abspath(__file__))
+    path = os.path.join(here, "libgsplat_synth.so")
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"{path} is not built: run `make -C {os.path.join(here, 'csrc')}`")
+    lib = C.CDLL(path)
+    lib.gsplat_synth_scene.restype = C.c_int
+    lib.gsplat_synth_scene.argtypes = [C.c_uint64, C.c_size_t, C.POINTER(C.c_float)]
+    out = np.empty((n, 16), F32)
+    rc = lib.gsplat_synth_scene(seed, n, out.ctypes.data_as(C.POINTER(C.c_float)))
+    if rc:
+        raise RuntimeError(f"gsplat_synth_scene failed: {rc}")
+    return out
+
+
 # ---- scene cache (SURVEY §8f row 4; same file as apps/splat_b200.cpp --cache) -----------------------
 CACHE_MAGIC = b"GSPLB200"
 

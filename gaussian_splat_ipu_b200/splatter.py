@@ -77,6 +77,7 @@ SYMBOLS = {
     "gsplat_timer_begin": (C.c_int, [_vp]),
     "gsplat_timer_end": (C.c_int, [_vp, _fp]),
     "gsplat_launch_count": (C.c_uint64, []),
+    "gsplat_flush_l2": (C.c_int, [_vp]),
     "gsplat_concurrent_frames": (C.c_int, [_vp]),
     "gsplat_count_pairs": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
 }
@@ -348,6 +349,10 @@ class B200Splatter:
         prs = np.zeros(self.num_tiles, np.uint64)
         self._check(self.lib.gsplat_profile_tiles(self.h, C.byref(a), C.byref(b), cyc.ctypes.data, prs.ctypes.data))
         return int(a.value), int(b.value), cyc, prs
+
+    def flush_l2(self):
+        """Cold L2 before the next frame (scenes smaller than L2): 256 MB device write, synchronous."""
+        self._check(self.lib.gsplat_flush_l2(self.h))
 
     def postprocess_bgr8(self):
         self._check(self.lib.gsplat_postprocess_bgr8(self.h))

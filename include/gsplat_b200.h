@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define GSPLAT_ABI_VERSION 3
+#define GSPLAT_ABI_VERSION 4
 
 typedef enum gsplat_status {
   GSPLAT_OK = 0,
@@ -51,7 +51,8 @@ typedef struct gsplat_config {
                          /* must divide width/height                                          */
   float guard_factor;    /* clipSize, codelets.cpp:622 (15): bbox diagonal < 15 tile diagonals */
   int band_row_begin;    /* tile-row band [begin,end) this context renders (multi-GPU tile    */
-  int band_row_end;      /* bands); 0,0 = all rows                                */
+  int band_row_end;      /* bands); end = -1 (the default) = all rows; begin ==   */
+                         /* end is an empty band (a rank that got no rows)                    */
   int collect_timings;   /* record per-stage cudaEvents (gsplat_get_timings)                  */
   int debug_records;     /* K1 also writes the projected records for gsplat_read_projected    */
   size_t dup_capacity;   /* initial capacity of the (tile,Gaussian) duplicate buffers;        */
@@ -217,6 +218,9 @@ int gsplat_abi_version(void);
  * milliseconds between them. */
 int gsplat_timer_begin(gsplat_ctx *ctx);
 int gsplat_timer_end(gsplat_ctx *ctx, float *ms);
+/* Measurement hygiene for scenes smaller than the 126 MB L2: overwrites a 256 MB device scratch
+ * buffer (allocated on first use) and waits, so the next frame starts with a cold L2. */
+int gsplat_flush_l2(gsplat_ctx *ctx);
 /* Kernel launches issued by this library since load (all contexts); for bench accounting. */
 uint64_t gsplat_launch_count(void);
 /* Re-runs K5 on the last frame's lists in counting mode: *pairs = number of (pixel, Gaussian)

@@ -160,6 +160,34 @@ class Oracle:
             self._lattice_destroy(h)
         return counts, fb, totals, held
 
+    def lattice_time(self, g16, view, proj, fov, scale_div, W, H, warm=60, timed=5, spare_slots=600, chan_slots=75,
+                     tile_w=32, tile_h=20, threads=0):
+        """O1 "as shipped" timing (kind="reference" only): `warm` program runs so the lattice reaches
+        its (lossy) steady state, then `timed` runs on the clock.  Returns (seconds per frame,
+        rendered copies in the last frame)."""
+        import time
+        assert self.kind == "reference"
+        g16 = np.ascontiguousarray(g16, dtype=np.float32).reshape(-1, 16)
+        view = np.ascontiguousarray(view, dtype=np.float32).ravel()
+        proj = np.ascontiguousarray(proj, dtype=np.float32).ravel()
+        TA, TD = W // tile_w, H // tile_h
+        h = self._lattice_create(g16.ctypes.data_as(_fp), g16.shape[0], W, H, TA, TD, spare_slots, chan_slots)
+        try:
+            step = lambda: self._lattice_step(h, view.ctypes.data_as(_fp), proj.ctypes.data_as(_fp), fov, scale_div, threads)
+            for _ in range(warm):
+                step()
+            t0 = time.perf_counter()
+            for _ in range(timed):
+                step()
+            dt = (time.perf_counter() - t0) / max(timed, 1)
+            counts = np.zeros(TA * TD, np.uint32)
+            fb = np.zeros(W * H * 4, np.float32)
+            ms = (C.c_double * 2)()
+            self._lattice_get(h, counts.ctypes.data_as(C.POINTER(C.c_uint32)), fb.ctypes.data_as(_fp), ms)
+        finally:
+            self._lattice_destroy(h)
+        return dt, int(counts.sum())
+
     def conic_opacity(self, cov, opacity):
         cov = np.ascontiguousarray(cov, np.float32)
         out = np.empty(4, np.float32)

@@ -40,7 +40,7 @@ def test_library_exports_every_declared_symbol():
 def test_ctypes_mirror_binds_the_declared_set():
     assert sorted(sp.SYMBOLS) == declared_symbols()
     lib = sp.load_library()
-    assert lib.gsplat_abi_version() == 3
+    assert lib.gsplat_abi_version() == 4
 
 
 def test_config_defaults_are_the_reference_constants():
@@ -50,6 +50,7 @@ def test_config_defaults_are_the_reference_constants():
     # tile_config.hpp:5-15 (1280x720, 40x36 tiles of 32x20), codelets.cpp:622 (clipSize 15)
     assert (cfg.width, cfg.height, cfg.tile_w, cfg.tile_h) == (1280, 720, 32, 20)
     assert cfg.guard_factor == 15.0 and cfg.device == 0
+    assert (cfg.band_row_begin, cfg.band_row_end) == (0, -1)        # -1: all tile rows; (0, 0) is an empty band
     assert lib.gsplat_config_default(None) == -1
 
 
@@ -77,6 +78,29 @@ def test_synth_scene_is_deterministic_and_in_spec():
     assert np.allclose(a[:, :3].max(0) + a[:, :3].min(0), 0, atol=1e-5)
     # a prefix of a longer scene is the same stream
     assert np.array_equal(sp.synth_scene(100, 7)[:, 4:15], sp.synth_scene(200, 7)[:100, 4:15])
+
+
+def test_host_only_synth_library_is_the_same_generator():
+    """libgsplat_synth.so (csrc/synth.cpp built with g++, no CUDA: what bench.py's CPU reference arm
+    loads so that it maps no product library) emits bit-identical records to gsplat_synth_scene of
+    the product library."""
+    from gaussian_splat_ipu_b200 import scene as sc
+    for n, seed in ((1, 1), (4097, 0xB2000006), (50000, 7)):
+        a, b = sc.synth_scene(n, seed), sp.synth_scene(n, seed)
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+def test_reference_arm_does_not_map_the_product_library():
+    """bench.py --impl reference builds its scene without dlopen-ing libgsplat_b200.so."""
+    import subprocess
+    import sys
+    code = ("import sys; sys.argv=['bench.py','--impl','reference','--workload','synthetic-200k-720p','--steps','2','--warmup','1'];"
+            "import runpy\n"
+            "try:\n runpy.run_path('bench.py', run_name='__main__')\nexcept SystemExit: pass\n"
+            "maps=open('/proc/self/maps').read()\n"
+            "sys.stderr.write('MAPPED' if 'libgsplat_b200' in maps else 'CLEAN')")
+    r = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stderr.strip().endswith("CLEAN"), r.stderr[-2000:]
 
 
 @pytest.mark.skipif(have_gpu(), reason="checks the no-GPU failure mode")
@@ -120,6 +144,29 @@ def _build_shim_smoke(tmpdir):
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     return exe
+
+
+def test_host_only_synth_library_is_the_same_generator():
+    """libgsplat_synth.so (csrc/synth.cpp built with g++, no CUDA: what bench.py's CPU reference arm
+    loads so that it maps no product library) emits bit-identical records to gsplat_synth_scene of
+    the product library."""
+    from gaussian_splat_ipu_b200 import scene as sc
+    for n, seed in ((1, 1), (4097, 0xB2000006), (50000, 7)):
+        a, b = sc.synth_scene(n, seed), sp.synth_scene(n, seed)
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+def test_reference_arm_does_not_map_the_product_library():
+    """bench.py --impl reference builds its scene without dlopen-ing libgsplat_b200.so."""
+    import subprocess
+    import sys
+    code = ("import sys; sys.argv=['bench.py','--impl','reference','--workload','synthetic-200k-720p','--steps','2','--warmup','1'];"
+            "import runpy\n"
+            "try:\n runpy.run_path('bench.py', run_name='__main__')\nexcept SystemExit: pass\n"
+            "maps=open('/proc/self/maps').read()\n"
+            "sys.stderr.write('MAPPED' if 'libgsplat_b200' in maps else 'CLEAN')")
+    r = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stderr.strip().endswith("CLEAN"), r.stderr[-2000:]
 
 
 @pytest.mark.skipif(have_gpu(), reason="checks the no-GPU failure mode")
