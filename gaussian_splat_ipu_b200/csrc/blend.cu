@@ -9,239 +9,357 @@
 //   test_T = T (1 - alpha);  test_T < 1e-4 -> stop this pixel (the stopping Gaussian is not added);
 //   C += colour * alpha * T over all FOUR channels (4th = opacity);  T = test_T.
 // There is no per-pixel bbox test in the reference: a Gaussian contributes to exactly the pixels
-// of the 32x20 tiles its rectangle covers, so the CTA *is* the semantic tile.
+// of the 32x20 tiles its rectangle covers, so the CTA *is* the semantic tile (or a column strip).
 //
-// Mapping: one CTA per tile (or column strip of it), one warp per 8 x 4 pixel BLOCK, one pixel per
-// thread in registers.  The list is staged through shared memory in batches of records gathered
-// by index; the staging thread also derives, per Gaussian, the rows and 8-pixel column blocks of
-// the part on which alpha >= 1/255 is possible at all (extent of the ellipse
-// power >= ln(1/(255 opacity)), conservative).  Each warp ballots over those extents and only
-// walks the Gaussians that can touch its block: skipped pairs are exactly pairs the reference loop
-// `continue`s over, so the result is unchanged while small splats cost ~nothing on the blocks
-// they miss.
-// exp() is ex2.approx.ftz on a log2e-prescaled conic.  FP32-pipe bound; no tensor cores (each
-// pair has its own quadratic form).  Stores are four 128 B row segments per warp.
+// BIT-EXACT blend chain.  The three tests above are discontinuities: a last-bit difference in
+// alpha moves T, and T * (1 - alpha) < 1e-4 then flips for pixels that sit on the threshold —
+// stacks of opaque splats (alpha capped at 0.99, T = 1 -> 0.01 -> 1e-4) sit there systematically,
+// and one flip changes a pixel by up to colour * 0.99 * 0.01, beyond the 1/255 parity bar
+// (measured on the shipped PLY orbit: 10 of 256 frames with a fused / ex2.approx evaluation).
+// Every value that feeds a decision or the accumulators is therefore computed with the
+// reference's operations in the reference's order: separately rounded f32 products and sums (this
+// file is compiled with -fmad=false) and exp() as the host libm computes it (exp_ref,
+// gsplat_internal.h).  The framebuffer is bit-identical to the host-compiled reference's.
+//
+// What makes that affordable is a conservative, FUSED pre-test: q = d^T Q d evaluated with two FMAs
+// against the per-Gaussian bound qmax (K1) rejects the pairs whose alpha is certainly < 1/255 —
+// the vast majority — and only the surviving lanes run the exact chain.
+//
+// Mapping: one CTA per part of a tile (a column strip), one CONSUMER warp per 8 x 4 pixel block
+// with one pixel per thread in registers, and one PRODUCER warp.  The producer streams the tile's
+// list through a shared-memory ring: per list entry ONE 48-byte bulk copy (cp.async.bulk, the TMA
+// unit; SASS UBLKCP) of the K1 record, completion counted in bytes by an mbarrier per ring stage.
+// Consumer warps wait on a stage's "full" barrier, test the staged entries against their block
+// (lane = entry: box of the alpha >= 1/255 ellipse vs the block, one ballot), walk the hits, and
+// release the stage through its "empty" barrier.  No CTA-wide barrier inside the loop: a warp
+// whose block few splats reach runs ahead of its neighbours by up to the ring depth.
+// FP32-pipe bound; no tensor cores (each pair has its own quadratic form).
 #include "gsplat_internal.h"
 
 namespace gsplat {
 
 unsigned long long g_launches = 0;
 
-constexpr int BLEND_MAX_ROWS = 32;
-constexpr float LOG2E = 1.4426950408889634f;
 constexpr float ALPHA_MIN = 1.0f / 255.0f;
 
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
+#ifndef GSPLAT_BLEND_STAGES
+#define GSPLAT_BLEND_STAGES 4
+#endif
+#ifndef GSPLAT_BLEND_BATCH
+#define GSPLAT_BLEND_BATCH 64
+#endif
+constexpr int BLEND_STAGES = GSPLAT_BLEND_STAGES;    // ring depth
+constexpr int BLEND_BATCH = GSPLAT_BLEND_BATCH;      // list entries per ring stage (multiple of 32)
+static_assert(BLEND_BATCH % 32 == 0, "consumers walk a stage in chunks of 32 entries");
+constexpr int BLEND_MAX_WARPS = 20;                  // consumer warps of an undivided 32 x 20 tile
+// How the producer warp moves a record into the ring:
+//   1  cp.async.bulk (TMA unit, SASS UBLKCP): one 48-byte copy per entry, bytes counted by the
+//      stage's mbarrier.  UBLKCP takes its addresses from UNIFORM registers, so a warp issues its 32
+//      copies one lane at a time (ELECT / R2UR loop, 8 instructions per entry).
+//   0  cp.async (SASS LDGSTS): three 16-byte copies per entry with per-lane addresses, the lane's
+//      completion delivered to the stage's mbarrier by cp.async.mbarrier.arrive.noinc.
+// Both are kept (-DGSPLAT_BLEND_TMA=0/1); DESIGN.md §4 has the measurement that picked the default.
+#ifndef GSPLAT_BLEND_TMA
+#define GSPLAT_BLEND_TMA 0
+#endif
+// Inner loop: 1 = per-pixel entry sets (phase A pre-test per entry, phase B exact chain per lane),
+// 0 = entry by entry (each surviving entry runs the exact chain for the lanes it reaches).
+#ifndef GSPLAT_BLEND_LANELIST
+#define GSPLAT_BLEND_LANELIST 1
+#endif
+constexpr uint32_t BLEND_FULL_ARRIVALS = GSPLAT_BLEND_TMA ? 1u : 32u;   // arrivals that complete a "full" phase
+
+struct BlendSmem {
+  float4 ring[BLEND_STAGES][BLEND_BATCH * 3];        // 48 B per entry: rec[3g .. 3g+2]
+  unsigned long long full[BLEND_STAGES];             // mbarrier: the stage's bytes have landed
+  unsigned long long empty[BLEND_STAGES];            // mbarrier: every consumer warp is done with the stage
+  unsigned long long exp_tab[32];                    // exp_ref's 2^(k/32) table
+  uint32_t warps_done;                               // consumer warps whose 32 pixels have all stopped
+  uint32_t stop;                                     // producer: nothing more will be staged
+};
+
+// ---- mbarrier / bulk-copy primitives (PTX ISA 8.x, sm_90+) ---------------------------------------
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_addr(bar)),
+      "r"(parity)
+      : "memory");
+}
+// 48-byte global -> shared bulk copy, completion signalled on `bar` in bytes (complete_tx)
+__device__ __forceinline__ void bulk_copy_48(void *dst, const void *src, unsigned long long *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 48, [%2];" ::"r"(smem_addr(dst)),
+               "l"(src), "r"(smem_addr(bar))
+               : "memory");
+}
+// 16-byte global -> shared asynchronous copy (L2 only: the record is not re-read by this SM)
+__device__ __forceinline__ void async_copy_16(void *dst, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(dst)), "l"(src) : "memory");
+}
+// the executing thread's earlier cp.async copies arrive on `bar` when they have completed; the
+// pending count is NOT incremented: the arrival is one of the barrier's expected arrivals
+__device__ __forceinline__ void async_copies_arrive(unsigned long long *bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_volatile_shared(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_addr(p)) : "memory");
+  return v;
 }
 
-// Shared-memory batch, blockDim.x entries of each (dynamic, sized by the launcher):
-//   sA float4: mean.x, mean.y, -0.5*log2e*A, -log2e*B     sB float4: -0.5*log2e*C, opacity, r, g
-//   sC float2: b, conservative log2 threshold (skip when power2 < it)
-//   sRows u16: row_lo | row_hi << 5 | mask of the part's 8-pixel column blocks << 10 ; 1: touches nothing
-#ifndef GSPLAT_BLEND_BATCH
-#define GSPLAT_BLEND_BATCH 2
-#endif
-constexpr uint32_t BLEND_BATCH = GSPLAT_BLEND_BATCH;   // list entries staged per thread and batch
-constexpr size_t BLEND_SMEM_PER_THREAD = BLEND_BATCH * (16 + 16 + 8 + 2);
+// One list entry against one pixel, in the reference's arithmetic (this TU is -fmad=false: every
+// * and + below is its own IEEE operation, as the host build of the codelet evaluates them).
+// codelets.cpp:389-410; returns true when the pixel stops at this entry.
+template <bool COUNT>
+__device__ __forceinline__ bool blend_exact(const float4 b, const float4 c, float dx, float dy,
+                                            const unsigned long long *exp_tab, float &T, float &Cr, float &Cg,
+                                            float &Cb, float &Ca, unsigned long long &n_blend) {
+  const float power = -0.5f * (b.x * dx * dx + b.z * dy * dy) - b.y * dx * dy;
+  if (power > 0.0f) return false;
+  const float e = c.x * exp_ref(power, exp_tab);
+  const float alpha = e < 0.99f ? e : 0.99f;        // glm::min(0.99f, e)
+  if (alpha < ALPHA_MIN) return false;
+  const float test_T = T * (1.f - alpha);
+  if (test_T < 0.0001f) return true;
+  Cr = Cr + c.y * alpha * T;                        // (colour * alpha) * T, then the accumulate
+  Cg = Cg + c.z * alpha * T;
+  Cb = Cb + c.w * alpha * T;
+  Ca = Ca + c.x * alpha * T;                        // 4th channel: the opacity itself (colour.w)
+  T = test_T;
+  if (COUNT) ++n_blend;
+  return false;
+}
 
-//
 // Depth slices (see duplicate.cu): the list of a tile may arrive in several consecutive pieces, one
 // launch each.  Between launches a pixel's state lives in the framebuffer (C) and in `tstate`
 // (T, or -1 once the pixel has stopped); a tile whose pixels have all stopped raises
 // tile_done[tile] so that later slices neither emit duplicates for it nor launch work on it.
 // FIRST: start from T = 1, C = 0.  LAST: no state is saved.
+// blockDim = (consumer warps + 1) * 32; the last warp is the producer.
 template <bool COUNT, bool FIRST, bool LAST>
-__global__ void __launch_bounds__(BLEND_MAX_ROWS * 32)
+__global__ void __launch_bounds__((BLEND_MAX_WARPS + 1) * 32)
 blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
              int tiles_across, int row_begin, int full_tile_h, int part_w, float4 *__restrict__ fb,
              float *__restrict__ tstate, TileState ts, const uint32_t *__restrict__ order,
              unsigned long long *__restrict__ pair_counters) {
-  extern __shared__ __align__(16) unsigned char blend_smem_raw[];
+  extern __shared__ __align__(128) unsigned char blend_smem_raw[];
+  BlendSmem &sm = *reinterpret_cast<BlendSmem *>(blend_smem_raw);
   const long long t_begin = COUNT ? clock64() : 0;
-  const uint32_t tid = threadIdx.x, lane = tid & 31, row = tid >> 5;
-  const uint32_t nthreads = blockDim.x;
-  float4 *sA = reinterpret_cast<float4 *>(blend_smem_raw);
-  float4 *sB = sA + BLEND_BATCH * nthreads;
-  float2 *sC = reinterpret_cast<float2 *>(sB + BLEND_BATCH * nthreads);
-  uint16_t *sRows = reinterpret_cast<uint16_t *>(sC + BLEND_BATCH * nthreads);
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t NW = (blockDim.x >> 5) - 1;           // consumer warps
   // a CTA blends a "part" of a semantic tile: all its rows, `part_w` = 32 / nsub of its columns (the
   // whole tile, or a column strip so that a crowded tile's list is walked by several SMs at
   // once); parts of one tile are neighbours in the grid.  A warp owns an 8 x 4 pixel block: a splat
   // a few pixels across then occupies a third of the lanes of the warps it reaches, where a
   // 32 x 1 pixel row would leave nine lanes in ten idle.
   const uint32_t nsub = (uint32_t)(32 / part_w), sub = blockIdx.x % nsub;
-  const uint32_t cbn = (uint32_t)part_w / 8u;            // 8-pixel column blocks per part
-  const uint32_t cb = row % cbn, rb = row / cbn;         // `row` = warp index: its block
-  const uint32_t x_local = sub * (uint32_t)part_w + cb * 8u + (lane & 7u), y_local = rb * 4u + (lane >> 3);
-  const bool valid = y_local < (uint32_t)full_tile_h;    // tile heights that are no multiple of 4
   // tiles are taken longest list first (tile_order_kernel) so the long ones do not start last
   const uint32_t tile = order[blockIdx.x / nsub] + (uint32_t)row_begin * tiles_across;
   const uint2 range = ranges[tile];
   const uint32_t n = range.y - range.x;
   const uint32_t part = tile * nsub + sub;
   if (!FIRST && (n == 0 || ts.part_done[part])) return;   // nothing new for this part: its state stands
-  // a10 layout: tile-major, row-major inside the tile
-  const size_t px = (size_t)tile * (32 * full_tile_h) + (size_t)(valid ? y_local : 0u) * 32 + x_local;
 
-  const uint32_t tcol = tile % tiles_across, trow = tile / tiles_across;
-  const float xp0 = (float)(tcol * 32u + sub * (uint32_t)part_w);   // first pixel column of the part
-  const float xf = (float)(tcol * 32u + x_local);
-  const float ty0 = (float)(trow * full_tile_h);
-  const float yf = ty0 + (float)y_local;
-  const int tile_h = full_tile_h;
-
-  float T = 1.f, Cr = 0.f, Cg = 0.f, Cb = 0.f, Ca = 0.f;
-  bool done = !valid;
-  if (!FIRST && valid) {
-    const float4 c = fb[px];
-    Cr = c.x; Cg = c.y; Cb = c.z; Ca = c.w;
-    T = tstate[px];
-    done = T < 0.f;
+  if (tid == 0) {
+    for (int s = 0; s < BLEND_STAGES; ++s) { mbar_init(&sm.full[s], BLEND_FULL_ARRIVALS); mbar_init(&sm.empty[s], NW); }
+    sm.warps_done = 0;
+    sm.stop = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  uint32_t stop_at = done ? 0u : n;   // COUNT: list entries this pixel visits (reference semantics)
-  unsigned long long n_blend = 0;  // COUNT
+  if (tid < 32) sm.exp_tab[tid] = EXPF_TAB[tid];
+  __syncthreads();
 
-  const uint32_t batch = BLEND_BATCH * nthreads;   // list entries staged per barrier pair
-  for (uint32_t base = 0; base < n; base += batch) {
-    // ---- stage one batch: gather the record, prescale, derive the row range ----------------
+  const uint32_t nbatch = (n + BLEND_BATCH - 1) / BLEND_BATCH;
+  const uint32_t tcol = tile % tiles_across, trow = tile / tiles_across;
+
+  if (warp == NW) {
+    // ---- producer: the tile's list, BLEND_BATCH entries per stage, one bulk copy per entry -------
+    for (uint32_t it = 0; it < nbatch; ++it) {
+      const uint32_t stage = it % BLEND_STAGES, use = it / BLEND_STAGES;
+      mbar_wait(&sm.empty[stage], (use & 1u) ^ 1u);        // first use of a stage: passes at once
+      if (ld_volatile_shared(&sm.warps_done) == NW) {      // every pixel of the part has stopped
+        if (lane == 0) *reinterpret_cast<volatile uint32_t *>(&sm.stop) = 1u;
+        __syncwarp();
+        if (lane < BLEND_FULL_ARRIVALS) mbar_arrive(&sm.full[stage]);   // releases the consumers waiting on this stage
+        break;
+      }
+      const uint32_t base = it * BLEND_BATCH, cnt = min((uint32_t)BLEND_BATCH, n - base);
+#if GSPLAT_BLEND_TMA
+      if (lane == 0) mbar_arrive_expect_tx(&sm.full[stage], cnt * 48u);
+      __syncwarp();
+#endif
 #pragma unroll
-    for (uint32_t sb = 0; sb < BLEND_BATCH; ++sb) {
-    const uint32_t slot = sb * nthreads + tid, j = base + slot;
-    if (j < n) {
-      const uint32_t g = vals[range.x + j];
-      const float4 *r = p.rec + (size_t)g * 3;   // 48 contiguous bytes: two sectors of one line
-      const float4 a = __ldg(r);
-      const float4 b = __ldg(r + 1);
-      const float cb = __ldg(&r[2].x);
-      const float A = a.z, B = a.w, C = b.x, op = b.y;
-      uint32_t lo = 1, hi = 0, cmask = 0xfu;
-      float thr2 = __int_as_float(0x7f800000);   // +inf: never passes
-      if (op * 255.0f > 1.0f) {                  // otherwise alpha = op*exp(<=0) < 1/255 everywhere
-        const float L2 = __log2f(op * 255.0f);   // power2 >= -L2  <=>  alpha >= 1/255
-        thr2 = -L2 - 0.02f;
-        lo = 0; hi = (uint32_t)tile_h - 1;
-        const float det = A * C - B * B;
-        if (det > 0.f && A > 0.f) {
-          // ellipse d^T Q d <= 2 ln(255 op): half-height sqrt(2L * A / det); padded
-          const float hy = sqrtf(2.0f * 0.6931472f * L2 * A / det) * 1.001f + 0.02f;
-          const float flo = ceilf(a.y - hy - ty0), fhi = floorf(a.y + hy - ty0);
-          if (fhi < 0.f || flo > (float)(tile_h - 1)) { lo = 1; hi = 0; }
-          else { lo = flo > 0.f ? (uint32_t)flo : 0u; hi = fhi < (float)(tile_h - 1) ? (uint32_t)fhi : (uint32_t)tile_h - 1; }
-          // Tighten to the rows the ellipse reaches INSIDE this tile's 32 columns: on row y the
-          // quadratic form is smallest at dx* = clamp(-B dy / A, [dx of last column, dx of first]);
-          // rows whose minimum already exceeds the bound (with margin) hold no pixel with
-          // alpha >= 1/255.  The set of passing rows is an interval (convexity): trim both ends.
-          const float bound = 2.0f * 0.6931472f * (L2 + 0.02f) * 1.001f + 1e-4f;
-          const float dxa = a.x - (xp0 + (float)(part_w - 1)), dxb = a.x - xp0, invA = 1.0f / A;
-          auto reaches = [&](uint32_t rrow) {
-            const float dy = a.y - (ty0 + (float)rrow);
-            const float dx = fminf(fmaxf(-B * dy * invA, dxa), dxb);
-            return A * dx * dx + 2.0f * B * dx * dy + C * dy * dy <= bound;
-          };
-          while (lo <= hi && !reaches(lo)) ++lo;
-          while (hi > lo && !reaches(hi)) --hi;
-          if (lo > hi) { lo = 1; hi = 0; }
-          // the 8-pixel column blocks of the part the ellipse reaches: half-width sqrt(2L * C / det)
-          if (lo <= hi && C > 0.f) {
-            const float hx = sqrtf(2.0f * 0.6931472f * L2 * C / det) * 1.001f + 0.02f;
-            const float fl = ceilf(a.x - hx - xp0), fh = floorf(a.x + hx - xp0);
-            if (fh < 0.f || fl > (float)(part_w - 1)) { lo = 1; hi = 0; }
-            else if (fl == fl && fh == fh) {
-              const uint32_t b0 = fl > 0.f ? (uint32_t)fl >> 3 : 0u;
-              const uint32_t b1 = fh < (float)(part_w - 1) ? (uint32_t)fh >> 3 : (uint32_t)(part_w - 1) >> 3;
-              cmask = ((2u << b1) - 1u) & ~((1u << b0) - 1u);
-            }
-          }
+      for (uint32_t j = lane; j < (uint32_t)BLEND_BATCH; j += 32) {
+        if (j < cnt) {
+          const uint32_t g = __ldg(&vals[range.x + base + j]);
+          const float4 *src = p.rec + (size_t)g * 3;
+          float4 *dst = &sm.ring[stage][j * 3];
+#if GSPLAT_BLEND_TMA
+          bulk_copy_48(dst, src, &sm.full[stage]);
+#else
+          async_copy_16(dst, src); async_copy_16(dst + 1, src + 1); async_copy_16(dst + 2, src + 2);
+#endif
         }
       }
-      sA[slot] = make_float4(a.x, a.y, -0.5f * LOG2E * A, -LOG2E * B);
-      sB[slot] = make_float4(-0.5f * LOG2E * C, op, b.z, b.w);
-      sC[slot] = make_float2(cb, thr2);
-      sRows[slot] = (uint16_t)(lo > hi ? 1u : lo | (hi << 5) | (cmask << 10));
+#if !GSPLAT_BLEND_TMA
+      async_copies_arrive(&sm.full[stage]);   // every lane: one of the 32 arrivals, once its copies have landed
+#endif
     }
+  } else {
+    // ---- consumers ---------------------------------------------------------------------------
+    const uint32_t cbn = (uint32_t)part_w / 8u;            // 8-pixel column blocks per part
+    const uint32_t cb = warp % cbn, rb = warp / cbn;       // this warp's block
+    const uint32_t x_local = sub * (uint32_t)part_w + cb * 8u + (lane & 7u), y_local = rb * 4u + (lane >> 3);
+    const bool valid = y_local < (uint32_t)full_tile_h;    // tile heights that are no multiple of 4
+    // a10 layout: tile-major, row-major inside the tile
+    const size_t px = (size_t)tile * (32 * full_tile_h) + (size_t)(valid ? y_local : 0u) * 32 + x_local;
+    const float xf = (float)(tcol * 32u + x_local);
+    const float yf = (float)(trow * full_tile_h) + (float)y_local;
+    // centre of the warp's 8 x 4 block (pixels x0..x0+7, y0..y0+3)
+    const float bcx = (float)(tcol * 32u + sub * (uint32_t)part_w + cb * 8u) + 3.5f;
+    const float bcy = (float)(trow * full_tile_h + rb * 4u) + 1.5f;
+
+    float T = 1.f, Cr = 0.f, Cg = 0.f, Cb = 0.f, Ca = 0.f;
+    bool done = !valid;
+    if (!FIRST && valid) {
+      const float4 c = fb[px];
+      Cr = c.x; Cg = c.y; Cb = c.z; Ca = c.w;
+      T = tstate[px];
+      done = T < 0.f;
     }
-    __syncthreads();
-    const uint32_t m = min(batch, n - base);
-    if (!__all_sync(0xffffffffu, done)) {
-      for (uint32_t c0 = 0; c0 < m; c0 += 32) {
-        const uint32_t jj = c0 + lane;
-        uint32_t rr = jj < m ? sRows[jj] : 1u;   // 1 = lo 1, hi 0: empty
-        uint32_t mask = __ballot_sync(0xffffffffu, (rr & 31u) <= rb * 4u + 3u && ((rr >> 5) & 31u) >= rb * 4u &&
-                                                       ((rr >> (10u + cb)) & 1u));
-        // two list entries per turn: their loads, quadratic forms and ex2 overlap; they are then
-        // applied to the pixel strictly in list order
-        while (mask) {
-          const uint32_t k0 = c0 + __ffs(mask) - 1;
-          mask &= mask - 1;
-          const bool two = mask != 0;
-          const uint32_t k1 = two ? c0 + __ffs(mask) - 1 : k0;
-          mask &= mask - 1;
-          const float4 a0 = sA[k0], a1 = sA[k1];
-          const float4 b0 = sB[k0], b1 = sB[k1];
-          const float2 e0 = sC[k0], e1 = sC[k1];
-          const float dx0 = a0.x - xf, dy0 = a0.y - yf, dx1 = a1.x - xf, dy1 = a1.y - yf;
-          // power * log2e = dx*(hA*dx + nB*dy) + hC*dy*dy
-          const float p0 = fmaf(b0.x * dy0, dy0, dx0 * fmaf(a0.w, dy0, a0.z * dx0));
-          const float p1 = fmaf(b1.x * dy1, dy1, dx1 * fmaf(a1.w, dy1, a1.z * dx1));
-          const bool v0 = p0 <= 0.f && p0 >= e0.y, v1 = two && p1 <= 0.f && p1 >= e1.y;
-          const float al0 = v0 ? fminf(0.99f, b0.y * ex2_approx(p0)) : 0.f;
-          const float al1 = v1 ? fminf(0.99f, b1.y * ex2_approx(p1)) : 0.f;
-          if (!done && al0 >= ALPHA_MIN) {
-            const float test_T = T * (1.f - al0);
-            if (test_T < 0.0001f) {
-              done = true;
-              if (COUNT) stop_at = base + k0 + 1;
-            } else {
-              const float w = al0 * T;
-              Cr = fmaf(b0.z, w, Cr); Cg = fmaf(b0.w, w, Cg); Cb = fmaf(e0.x, w, Cb); Ca = fmaf(b0.y, w, Ca);
-              T = test_T;
-              if (COUNT) ++n_blend;
+    uint32_t stop_at = done ? 0u : n;   // COUNT: list entries this pixel visits (reference semantics)
+    unsigned long long n_blend = 0;     // COUNT
+    bool warp_done = __all_sync(0xffffffffu, done);
+    if (warp_done && lane == 0) atomicAdd(&sm.warps_done, 1u);
+
+    for (uint32_t it = 0; it < nbatch; ++it) {
+      const uint32_t stage = it % BLEND_STAGES, use = it / BLEND_STAGES;
+      mbar_wait(&sm.full[stage], use & 1u);
+      if (ld_volatile_shared(&sm.stop)) break;
+      if (!warp_done) {
+        const uint32_t base = it * BLEND_BATCH, cnt = min((uint32_t)BLEND_BATCH, n - base);
+        const float4 *ring = sm.ring[stage];
+        for (uint32_t c0 = 0; c0 < cnt; c0 += 32) {
+          // lane = entry: does the box around its alpha >= 1/255 ellipse reach this warp's block?
+          const uint32_t jj = c0 + lane;
+          bool hit = false;
+          if (jj < cnt) {
+            const float4 a = ring[jj * 3];
+            hit = fabsf(a.x - bcx) <= a.z + 3.5f && fabsf(a.y - bcy) <= a.w + 1.5f;
+          }
+          uint32_t mask = __ballot_sync(0xffffffffu, hit);
+#if GSPLAT_BLEND_LANELIST
+          // Phase A, whole warp per entry: the fused pre-test q = A dx^2 + 2 B dx dy + C dy^2 against
+          // qmax (alpha < 1/255 beyond it) gives every pixel the set of chunk entries it must blend.
+          uint32_t smask = 0;
+          while (mask) {
+            const uint32_t l0 = __ffs(mask) - 1;
+            mask &= mask - 1;
+            const bool two = mask != 0;
+            const uint32_t l1 = two ? __ffs(mask) - 1 : l0;
+            mask &= mask - 1;
+            const float4 a0 = ring[(c0 + l0) * 3], b0 = ring[(c0 + l0) * 3 + 1];
+            const float4 a1 = ring[(c0 + l1) * 3], b1 = ring[(c0 + l1) * 3 + 1];
+            const float dx0 = a0.x - xf, dy0 = a0.y - yf, dx1 = a1.x - xf, dy1 = a1.y - yf;
+            const float q0 = fmaf(b0.z * dy0, dy0, dx0 * fmaf(b0.x, dx0, (b0.y + b0.y) * dy0));
+            const float q1 = fmaf(b1.z * dy1, dy1, dx1 * fmaf(b1.x, dx1, (b1.y + b1.y) * dy1));
+            smask |= (q0 <= b0.w ? 1u << l0 : 0u) | (two && q1 <= b1.w ? 1u << l1 : 0u);
+          }
+          if (done) smask = 0;
+          // Phase B, one pixel per lane: every lane walks ITS OWN entries in list order through the
+          // exact chain, so a turn of the loop blends up to 32 different (pixel, entry) pairs instead of
+          // one entry against the few pixels it reaches; turns = the longest per-pixel set.
+          while (__any_sync(0xffffffffu, smask != 0)) {
+            if (smask) {
+              const uint32_t kl = __ffs(smask) - 1;
+              smask &= smask - 1;
+              const float4 *e = ring + (c0 + kl) * 3;
+              const float2 mxy = *reinterpret_cast<const float2 *>(e);
+              if (blend_exact<COUNT>(e[1], e[2], mxy.x - xf, mxy.y - yf, sm.exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
+                done = true;
+                smask = 0;
+                if (COUNT) stop_at = base + c0 + kl + 1;
+              }
             }
           }
-          if (!done && al1 >= ALPHA_MIN) {
-            const float test_T = T * (1.f - al1);
-            if (test_T < 0.0001f) {
-              done = true;
-              if (COUNT) stop_at = base + k1 + 1;
-            } else {
-              const float w = al1 * T;
-              Cr = fmaf(b1.z, w, Cr); Cg = fmaf(b1.w, w, Cg); Cb = fmaf(e1.x, w, Cb); Ca = fmaf(b1.y, w, Ca);
-              T = test_T;
-              if (COUNT) ++n_blend;
+#else
+          // two list entries per turn: their loads and fused pre-tests overlap; they are then applied
+          // to the pixel strictly in list order
+          while (mask) {
+            const uint32_t k0 = c0 + __ffs(mask) - 1;
+            mask &= mask - 1;
+            const bool two = mask != 0;
+            const uint32_t k1 = two ? c0 + __ffs(mask) - 1 : k0;
+            mask &= mask - 1;
+            const float4 a0 = ring[k0 * 3], b0 = ring[k0 * 3 + 1];
+            const float4 a1 = ring[k1 * 3], b1 = ring[k1 * 3 + 1];
+            const float dx0 = a0.x - xf, dy0 = a0.y - yf, dx1 = a1.x - xf, dy1 = a1.y - yf;
+            // fused pre-test: q = A dx^2 + 2 B dx dy + C dy^2 against qmax (alpha < 1/255 beyond it)
+            const float q0 = fmaf(b0.z * dy0, dy0, dx0 * fmaf(b0.x, dx0, (b0.y + b0.y) * dy0));
+            const float q1 = fmaf(b1.z * dy1, dy1, dx1 * fmaf(b1.x, dx1, (b1.y + b1.y) * dy1));
+            const bool s0 = !done && q0 <= b0.w;
+            if (__any_sync(0xffffffffu, s0)) {
+              if (s0 && blend_exact<COUNT>(b0, ring[k0 * 3 + 2], dx0, dy0, sm.exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
+                done = true;
+                if (COUNT) stop_at = base + k0 + 1;
+              }
+            }
+            const bool s1 = two && !done && q1 <= b1.w;
+            if (__any_sync(0xffffffffu, s1)) {
+              if (s1 && blend_exact<COUNT>(b1, ring[k1 * 3 + 2], dx1, dy1, sm.exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
+                done = true;
+                if (COUNT) stop_at = base + k1 + 1;
+              }
             }
           }
+#endif
+          if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
         }
-        if (__all_sync(0xffffffffu, done)) break;
+        if (warp_done && lane == 0) atomicAdd(&sm.warps_done, 1u);   // before the release below
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.empty[stage]);
+    }
+
+    if (!LAST && valid) tstate[px] = done ? -1.f : T;
+    if (COUNT) {
+      unsigned long long n_visit = stop_at;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        n_visit += __shfl_xor_sync(0xffffffffu, n_visit, o);
+        n_blend += __shfl_xor_sync(0xffffffffu, n_blend, o);
+      }
+      if (lane == 0) {
+        atomicAdd(&pair_counters[0], n_visit); atomicAdd(&pair_counters[1], n_blend);
+        atomicAdd(&pair_counters[2 + 2 * (size_t)tile + 1], n_visit);            // per-tile profile tap
+        atomicAdd(&pair_counters[2 + 2 * (size_t)tile], (unsigned long long)(clock64() - t_begin) / NW);
       }
     }
-    // all pixels of the tile stopped -> the rest of the list cannot contribute
-    if (__syncthreads_and(done)) break;
+    if (valid) fb[px] = make_float4(Cr, Cg, Cb, Ca);
   }
   if (!LAST) {
-    if (valid) tstate[px] = done ? -1.f : T;
-    if (__syncthreads_and(done) && tid == 0) {
+    __syncthreads();   // every consumer warp has added itself to warps_done if its pixels have stopped
+    if (tid == 0 && sm.warps_done == NW) {
       ts.part_done[part] = 1;
       if (atomicAdd(&ts.parts_done[tile], 1u) + 1u == nsub) ts.tile_done[tile] = 1;   // last part of the tile to stop
     }
   }
-
-  if (COUNT) {
-    unsigned long long n_visit = stop_at;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      n_visit += __shfl_xor_sync(0xffffffffu, n_visit, o);
-      n_blend += __shfl_xor_sync(0xffffffffu, n_blend, o);
-    }
-    if (lane == 0) {
-      atomicAdd(&pair_counters[0], n_visit); atomicAdd(&pair_counters[1], n_blend);
-      atomicAdd(&pair_counters[2 + 2 * (size_t)tile + 1], n_visit);            // per-tile profile tap
-      atomicAdd(&pair_counters[2 + 2 * (size_t)tile], (unsigned long long)(clock64() - t_begin) / (unsigned)full_tile_h);
-    }
-  }
-  if (valid) fb[px] = make_float4(Cr, Cg, Cb, Ca);
 }
 
 // ---- launch order of the tiles: longest list first ---------------------------------------------
@@ -317,17 +435,15 @@ static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, cons
   if (rows <= 0) return;
   const int full_h = (int)fp.tile_h;
   const int part_w = 32 / split;                                  // columns per CTA (split is 1, 2 or 4)
-  const int threads = (part_w / 8) * ((full_h + 3) / 4) * 32;    // one warp per 8 x 4 pixel block
-  // dynamic smem sized for this part so that several CTAs fit per SM
-  const size_t smem = (size_t)threads * BLEND_SMEM_PER_THREAD;
+  const int warps = (part_w / 8) * ((full_h + 3) / 4);           // one consumer warp per 8 x 4 pixel block
   ++g_launches;
-  blend_kernel<COUNT, FIRST, LAST><<<rows * fp.tiles_across * split, threads, smem, st>>>(
+  blend_kernel<COUNT, FIRST, LAST><<<rows * fp.tiles_across * split, (warps + 1) * 32, sizeof(BlendSmem), st>>>(
       p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, full_h, part_w, fb_tiled, tstate, ts, order, pair_counters);
 }
 
 template <bool COUNT, bool FIRST, bool LAST> static cudaError_t blend_attr() {
   return cudaFuncSetAttribute(blend_kernel<COUNT, FIRST, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)(BLEND_MAX_ROWS * 32 * BLEND_SMEM_PER_THREAD));
+                              (int)sizeof(BlendSmem));
 }
 // Dynamic shared memory opt-in of every K5 variant on the CURRENT device (the attribute belongs to
 // the device's context: gsplat_create runs this once per device).

@@ -31,18 +31,19 @@ struct SceneSoA {
   uint32_t n;
 };
 
-// K1 output per Gaussian: one 48-byte AoS record (three float4, contiguous, so the K5 gather of a
-// record touches two 32 B sectors of one line instead of three lines), written for drawn
-// Gaussians only, plus a 32-bit depth key for EVERY Gaussian (culled = 0xffffffff, sorts last).
-//   rec[3g+0] = mean.x, mean.y, conic.x, conic.y
-//   rec[3g+1] = conic.z, opacity (0 when det == 0), r, g
-//   rec[3g+2] = b, clip z, rect {c0 | c1<<16}, rect {r0 | r1<<16}   (last two are uint bit patterns;
-//               the row pair is already clamped to this context's tile-row band)
+// K1 output per Gaussian: one 48-byte AoS record (three float4, contiguous: one 48-byte bulk copy
+// moves it into K5's shared-memory ring), written for drawn Gaussians only, plus a 32-bit depth
+// key for EVERY Gaussian (culled = 0xffffffff, sorts last).
+//   rec[3g+0] = mean.x, mean.y, hx, hy      half extents of the box around the ellipse alpha >= 1/255
+//                                           (-inf: never visible; +inf: no finite extent, always visited)
+//   rec[3g+1] = conic.x, conic.y, conic.z, qmax   Gaussian2D::ComputeConicOpacity's values; a pair whose
+//                                           quadratic form exceeds qmax has alpha < 1/255 (skipped)
+//   rec[3g+2] = opacity (0 when det == 0), r, g, b
 struct Projected {
   float4 *rec;
   uint32_t *depth_key;   // ~bits(clip z) for drawn Gaussians (z < 0  =>  key < 2^31), per Gaussian
-  uint2 *rect;           // {c0 | c1<<16, r0 | r1<<16} again, compact (8 B): K2 gathers it in depth
-                         // order, and a random 8 B read costs one 32 B sector instead of a 48 B record
+  uint2 *rect;           // tile rectangle {c0 | c1<<16, r0 | r1<<16}, rows clamped to this context's
+                         // band; RECT_EMPTY when not drawn.  Read by the counts, the selection and K2
 };
 // ---- chained scan with decoupled look-back (K2 and the slice selection) ------------------------
 // One 64-bit word per chain link: flag in the top two bits, value below, so one store publishes both.
@@ -108,6 +109,46 @@ __device__ __forceinline__ unsigned long long lb_exclusive_prefix(unsigned long 
   if (lane == 0) lb_store(&lookback[b], LB_PREFIX | (excl + total));
   return excl;
 }
+#endif
+
+#ifdef __CUDACC__
+// expf as the host libm computes it.  The reference's codelets call exp() on floats
+// (ipu_geometry.hpp:319-321); host-compiled, that is glibc's expf (sysdeps/ieee754/flt-32/e_expf.c,
+// glibc >= 2.27; the algorithm of ARM's optimized-routines): with N = 32,
+//   k = round(x * N / ln2),  r = x * N / ln2 - k,  exp(x) = 2^(k/N) * P(r),
+// 2^(k/N) from a 32-entry table of doubles (exponent bits added by integer arithmetic), P a cubic,
+// all in f64, rounded once to f32.  Restated here with the same table, constants and operation
+// order, so the result is bit-identical to the oracle's (a correctly rounded exp differs from it
+// for about one argument in 2000) at a fraction of the f64 work of exp(double).
+static __constant__ unsigned long long EXPF_TAB[32] = {
+    0x3ff0000000000000ull, 0x3fefd9b0d3158574ull, 0x3fefb5586cf9890full, 0x3fef9301d0125b51ull,
+    0x3fef72b83c7d517bull, 0x3fef54873168b9aaull, 0x3fef387a6e756238ull, 0x3fef1e9df51fdee1ull,
+    0x3fef06fe0a31b715ull, 0x3feef1a7373aa9cbull, 0x3feedea64c123422ull, 0x3feece086061892dull,
+    0x3feebfdad5362a27ull, 0x3feeb42b569d4f82ull, 0x3feeab07dd485429ull, 0x3feea47eb03a5585ull,
+    0x3feea09e667f3bcdull, 0x3fee9f75e8ec5f74ull, 0x3feea11473eb0187ull, 0x3feea589994cce13ull,
+    0x3feeace5422aa0dbull, 0x3feeb737b0cdc5e5ull, 0x3feec49182a3f090ull, 0x3feed503b23e255dull,
+    0x3feee89f995ad3adull, 0x3feeff76f2fb5e47ull, 0x3fef199bdd85529cull, 0x3fef3720dcef9069ull,
+    0x3fef5818dcfba487ull, 0x3fef7c97337b9b5full, 0x3fefa4afa2a490daull, 0x3fefd0765b6e4540ull,
+};
+__device__ __forceinline__ float exp_ref(float x, const unsigned long long *tab /* EXPF_TAB in shared memory */) {
+  if (!(x == x)) return x + x;
+  if (x > 88.72283172607421875f) return __int_as_float(0x7f800000);    // 0x1.62e42ep6f: overflow
+  if (x < -103.97207641601562500f) return 0.0f;                        // -0x1.9fe368p6f: underflow
+  constexpr double INVLN2N = 0x1.71547652b82fep+0 * 32.0, SHIFT = 0x1.8p+52;
+  constexpr double C0 = 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0, C1 = 0x1.ebfce50fac4f3p-3 / 32.0 / 32.0,
+                   C2 = 0x1.62e42ff0c52d6p-1 / 32.0;
+  const double z = INVLN2N * (double)x;
+  double kd = z + SHIFT;
+  const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+  kd -= SHIFT;
+  const double r = z - kd;
+  const double s = __longlong_as_double((long long)(tab[ki & 31ull] + (ki << 47)));
+  const double zz = C0 * r + C1, r2 = r * r;
+  double y = C2 * r + 1.0;
+  y = zz * r2 + y;
+  return (float)(y * s);
+}
+
 #endif
 
 constexpr uint32_t DEPTH_KEY_CULLED = 0xffffffffu;

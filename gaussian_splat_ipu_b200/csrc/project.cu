@@ -33,43 +33,6 @@ __device__ __forceinline__ M3 m3_t(const M3 &a) {
 }
 __device__ __forceinline__ float min_ref(float a, float b) { return a < b ? a : b; }   // ipu_geometry.hpp:329-331
 __device__ __forceinline__ float max_ref(float a, float b) { return a > b ? a : b; }   // ipu_geometry.hpp:325-327
-// expf as the host libm computes it.  The reference's codelets call exp() on floats
-// (ipu_geometry.hpp:319-321); host-compiled, that is glibc's expf (sysdeps/ieee754/flt-32/e_expf.c,
-// glibc >= 2.27; the algorithm of ARM's optimized-routines): with N = 32,
-//   k = round(x * N / ln2),  r = x * N / ln2 - k,  exp(x) = 2^(k/N) * P(r),
-// 2^(k/N) from a 32-entry table of doubles (exponent bits added by integer arithmetic), P a cubic,
-// all in f64, rounded once to f32.  Restated here with the same table, constants and operation
-// order, so the result is bit-identical to the oracle's (a correctly rounded exp differs from it
-// for about one argument in 2000) at a fraction of the f64 work of exp(double).
-__constant__ unsigned long long EXPF_TAB[32] = {
-    0x3ff0000000000000ull, 0x3fefd9b0d3158574ull, 0x3fefb5586cf9890full, 0x3fef9301d0125b51ull,
-    0x3fef72b83c7d517bull, 0x3fef54873168b9aaull, 0x3fef387a6e756238ull, 0x3fef1e9df51fdee1ull,
-    0x3fef06fe0a31b715ull, 0x3feef1a7373aa9cbull, 0x3feedea64c123422ull, 0x3feece086061892dull,
-    0x3feebfdad5362a27ull, 0x3feeb42b569d4f82ull, 0x3feeab07dd485429ull, 0x3feea47eb03a5585ull,
-    0x3feea09e667f3bcdull, 0x3fee9f75e8ec5f74ull, 0x3feea11473eb0187ull, 0x3feea589994cce13ull,
-    0x3feeace5422aa0dbull, 0x3feeb737b0cdc5e5ull, 0x3feec49182a3f090ull, 0x3feed503b23e255dull,
-    0x3feee89f995ad3adull, 0x3feeff76f2fb5e47ull, 0x3fef199bdd85529cull, 0x3fef3720dcef9069ull,
-    0x3fef5818dcfba487ull, 0x3fef7c97337b9b5full, 0x3fefa4afa2a490daull, 0x3fefd0765b6e4540ull,
-};
-__device__ __forceinline__ float exp_ref(float x, const unsigned long long *tab /* EXPF_TAB in shared memory */) {
-  if (!(x == x)) return x + x;
-  if (x > 88.72283172607421875f) return __int_as_float(0x7f800000);    // 0x1.62e42ep6f: overflow
-  if (x < -103.97207641601562500f) return 0.0f;                        // -0x1.9fe368p6f: underflow
-  constexpr double INVLN2N = 0x1.71547652b82fep+0 * 32.0, SHIFT = 0x1.8p+52;
-  constexpr double C0 = 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0, C1 = 0x1.ebfce50fac4f3p-3 / 32.0 / 32.0,
-                   C2 = 0x1.62e42ff0c52d6p-1 / 32.0;
-  const double z = INVLN2N * (double)x;
-  double kd = z + SHIFT;
-  const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
-  kd -= SHIFT;
-  const double r = z - kd;
-  const double s = __longlong_as_double((long long)(tab[ki & 31ull] + (ki << 47)));
-  const double zz = C0 * r + C1, r2 = r * r;
-  double y = C2 * r + 1.0;
-  y = zz * r2 + y;
-  return (float)(y * s);
-}
-
 template <int THREADS>
 __device__ __forceinline__ uint32_t block_sum(uint32_t v, uint32_t *smem /* THREADS/32 */) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -213,11 +176,33 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
             const float det_inv = 1.f / det;
             kx = covc * det_inv; ky = -covb * det_inv; kz = cova * det_inv; kw = col.w;
           }
+          // K5 record (gsplat_internal.h): mean, conic and opacity exactly as the reference's blend
+          // loop recomputes them per pixel (ComputeConicOpacity), plus two CONSERVATIVE culling aids:
+          // the half extents of the axis-aligned box around the ellipse alpha >= 1/255, which K5's
+          // warps test against their 8x4 pixel blocks, and qmax, the largest value of the quadratic
+          // form d^T Q d at which alpha >= 1/255 is possible.  Pairs skipped through them are pairs
+          // the reference loop `continue`s over (codelets.cpp:400-403).
+          float qmax = __int_as_float(0xff800000);                     // -inf: no pixel ever passes
+          float hx = __int_as_float(0xff800000), hy = hx;              // -inf: touches no block
+          if (kw * 255.0f > 1.0f) {                  // otherwise alpha = op * exp(<= 0) < 1/255 everywhere
+            const float L = __logf(kw * 255.0f);     // power >= -L  <=>  op * exp(power) >= 1/255
+            // margin: K5 evaluates the form fused, the reference's power unfused, and for thin splats the
+            // three terms cancel (each up to ~1e5 where the form itself is ~20)
+            qmax = 2.0f * L * 1.01f + 0.5f;
+            hx = hy = __int_as_float(0x7f800000);    // indefinite form: no extent, every block is visited
+            if (det > 0.f && cova > 0.f && covc > 0.f) {
+              // ellipse d^T Q d <= 2L with Q = cov^-1: half-width sqrt(2L cov.xx), half-height
+              // sqrt(2L cov.yy) — from the covariance itself, NOT from the conic: C / (A C - B^2)
+              // cancels catastrophically for thin splats and undershoots the extent
+              hx = sqrtf(2.0f * L * cova) * 1.01f + 0.5f;
+              hy = sqrtf(2.0f * L * covc) * 1.01f + 0.5f;
+              if (!(hx == hx) || !(hy == hy)) hx = hy = __int_as_float(0x7f800000);
+            }
+          }
           float4 *r = out.rec + (size_t)i * 3;
-          r[0] = make_float4(px, py, kx, ky);
-          r[1] = make_float4(kz, kw, col.x, col.y);
-          r[2] = make_float4(col.z, cz, __uint_as_float((uint32_t)c0 | ((uint32_t)c1 << 16)),
-                             __uint_as_float((uint32_t)e0 | ((uint32_t)e1 << 16)));
+          r[0] = make_float4(px, py, hx, hy);
+          r[1] = make_float4(kx, ky, kz, qmax);
+          r[2] = make_float4(kw, col.x, col.y, col.z);
           rect_out = make_uint2((uint32_t)c0 | ((uint32_t)c1 << 16), (uint32_t)e0 | ((uint32_t)e1 << 16));
         }
       }
@@ -253,12 +238,8 @@ inject_kernel(const float *__restrict__ depth, const int32_t *__restrict__ rect4
       touched = clamp_rect(c0, c1, r0, r1, fp);
       const int e0 = r0 < fp.row_begin ? fp.row_begin : r0, e1 = r1 > fp.row_end - 1 ? fp.row_end - 1 : r1;
       if (touched) {
-        float4 c = out.rec[(size_t)i * 3 + 2];
-        c.y = z = depth[i];
-        c.z = __uint_as_float((uint32_t)c0 | ((uint32_t)c1 << 16));
-        c.w = __uint_as_float((uint32_t)e0 | ((uint32_t)e1 << 16));
-        out.rec[(size_t)i * 3 + 2] = c;
-        out.rect[i] = make_uint2(__float_as_uint(c.z), __float_as_uint(c.w));
+        z = depth[i];
+        out.rect[i] = make_uint2((uint32_t)c0 | ((uint32_t)c1 << 16), (uint32_t)e0 | ((uint32_t)e1 << 16));
       }
     }
     out.depth_key[i] = touched ? ~__float_as_uint(z) : DEPTH_KEY_CULLED;

@@ -15,7 +15,8 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libgsplat_b200.so")
+# GSPLAT_LIB: an experiment build of the same library (csrc/Makefile `variant`), for A/B measurements
+LIB_PATH = os.environ.get("GSPLAT_LIB") or os.path.join(HERE, "libgsplat_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 
 NUM_TIMINGS = 8

@@ -58,7 +58,10 @@ class Frame:
 
 
 class Oracle:
-    def __init__(self, kind: str = "port"):
+    def __init__(self, kind: str = "port", tie_order: str = "canonical"):
+        """tie_order: how Gaussians with bit-identical clip z are ordered in the blend — "canonical"
+        (z, then gid: the parity contract) or "quicksort" (gid-order fill, the
+        reference's unstable quicksort decides; the lists are reported canonically either way)."""
         if kind == "reference":
             if not os.path.exists(REF_SO):
                 raise FileNotFoundError(REF_SO)
@@ -78,6 +81,10 @@ class Oracle:
         f("frame_get_framebuffer", None, [C.c_void_p, _fp])
         f("frame_get_timings", None, [C.c_void_p, C.POINTER(C.c_double)])
         f("num_threads", C.c_int, [])
+        f("set_tie_order", None, [C.c_int])
+        if tie_order not in ("canonical", "quicksort"):
+            raise ValueError(tie_order)
+        self.tie_order = tie_order
         f("conic_opacity", None, [_fp, C.c_float, _fp])
         f("tile_bounds", None, [C.c_int] * 4 + [C.c_uint, _fp])
         if kind == "reference":   # O1: the unmodified GSplat::compute over the 4-neighbour lattice
@@ -106,6 +113,7 @@ class Oracle:
         n = g16.shape[0]
         TA, TD = W // tile_w, H // tile_h
         assert TA * tile_w == W and TD * tile_h == H
+        self._set_tie_order(int(self.tie_order == "quicksort"))   # library-global: set per call
         h = self._frame_create(g16.ctypes.data_as(_fp), n, view.ctypes.data_as(_fp), proj.ctypes.data_as(_fp),
                                fov, scale_div, W, H, TA, TD, int(render), threads)
         try:

@@ -62,6 +62,10 @@ extern "C" {
 // derives the render predicate + converged tile rectangle.
 // g16: n records of 16 floats (the reference's Gaussian3D: mean4 colour4 rot4 scale3 gid).
 // mv/proj: glm column-major 4x4 (what IpuSplatter::updateModelView receives).
+// 0: ties in clip z blend in (z, gid) order (the parity contract); 1: the reference's quicksort decides
+static int g_tie_order = 0;
+void ref_set_tie_order(int quicksort_decides) { g_tie_order = quicksort_decides ? 1 : 0; }
+
 void *ref_frame_create(const float *g16, std::size_t n, const float *mv, const float *proj,
                        float fov, float scale_div, int W, int H, int TA, int TD, int do_render,
                        int nthreads) {
@@ -162,12 +166,27 @@ void *ref_frame_create(const float *g16, std::size_t n, const float *mv, const f
     return f;
   }
 
-  // Blend: per tile, fill a GSplat vertex's gaus2D in gid order and call the reference's own
-  // renderTile (its quicksort, ComputeConicOpacity and blend loop run unmodified).
+  // Blend: per tile, fill a GSplat vertex's gaus2D and call the reference's own renderTile
+  // (ComputeConicOpacity and the blend loop run unmodified).
+  //
+  // Tie order.  Different Gaussians do share a clip-space z bit for bit (about 150 pairs per frame on
+  // the shipped PLYs), the reference's quicksort is unstable (codelets.cpp:303-344), and on the IPU
+  // the buffer it sorts is in lattice ARRIVAL order, which changes from run to run: the order of tied
+  // entries is unspecified in the reference.  It is not harmless either: swapping two tied entries
+  // moves T by an ulp, and pixels that sit on the T * (1 - alpha) < 1e-4 stop (stacks of opaque
+  // splats: 1 -> 0.01 -> 1e-4) then flip by up to colour * 0.99 * 0.01.  The parity contract
+  //  fixes the order of ties as (z ascending, gid ascending):
+  //   g_tie_order == 0 (default): the list is put in that order BEFORE it is handed to the vertex,
+  //     and `indices` is bound with a single element, for which the reference's own sortBuffer
+  //     returns without sorting (codelets.cpp:348-350: end >= indices.size() - 1) — an ordered list
+  //     is also the O(n^2) case of its last-element-pivot quicksort (minutes on a 363k-entry tile);
+  //   g_tie_order == 1: gid-order fill, the reference's quicksort runs and decides the ties (what
+  //     round 1 did; kept to measure how far the two orders are apart).
   t0 = now_ms();
   f->fb.assign(std::size_t(W) * H * 4, 0.f);
   const std::size_t tilePix = std::size_t(tw) * std::size_t(th);
   const std::size_t g2stride = sizeof(Gaussian2D);   // the codelet strides by sizeof in FLOATS (codelets.cpp:370,494)
+  const bool canonical = g_tie_order == 0;
 #pragma omp parallel num_threads(nthreads)
   {
     std::vector<float> gaus2D;
@@ -179,8 +198,11 @@ void *ref_frame_create(const float *g16, std::size_t n, const float *mv, const f
       const std::size_t cnt = f->counts[t];
       float *fbTile = &f->fb[std::size_t(t) * tilePix * 4];
       if (cnt == 0) continue;                          // codelets.cpp:501 (fb stays zero: colourFb)
+      auto b = f->lists.begin() + f->offsets[t], e = f->lists.begin() + f->offsets[t + 1];
+      auto by_z = [&](int32_t a, int32_t c) { return f->rec[a * 8 + 2] < f->rec[c * 8 + 2]; };
+      if (canonical) std::stable_sort(b, e, by_z);     // (z asc, gid asc): the list was in gid order
       gaus2D.assign((cnt + 2) * g2stride, 0.f);        // slot n is the all-zero sentinel (a8)
-      indices.assign(2 * cnt + 64, 0);
+      indices.assign(canonical ? 1 : 2 * cnt + 64, 0);
       for (std::size_t k = 0; k < cnt; ++k) {
         const std::size_t i = f->lists[f->offsets[t] + k];
         Gaussian3D g;
@@ -195,10 +217,8 @@ void *ref_frame_create(const float *g16, std::size_t n, const float *mv, const f
       v.localFb.bind(fbTile, tilePix * 4);
       v.tile_id.bind(tileId, 1);
       v.renderTile(cnt, tfb.getTileBounds(t));
-      // canonical (z asc, gid asc) list for parity checks; the reference's own quicksort order
-      // (unstable) was used for the pixels above.
-      auto b = f->lists.begin() + f->offsets[t], e = f->lists.begin() + f->offsets[t + 1];
-      std::stable_sort(b, e, [&](int32_t a, int32_t c) { return f->rec[a * 8 + 2] < f->rec[c * 8 + 2]; });
+      // the lists are reported in the canonical order in both modes
+      if (!canonical) std::stable_sort(b, e, by_z);
     }
   }
   f->blend_ms = now_ms() - t0;

@@ -6,17 +6,18 @@ sys.path.insert(0, '.')
 import numpy as np, bench
 from gaussian_splat_ipu_b200.splatter import B200Splatter
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 1920
-g, base, proj, W, H = bench.make_scene(bench.DEFAULT_WORKLOAD)
-views = [bench.view_for(base, k) for k in range(bench.ORBIT_VIEWS)]
+scn = bench.make_scene(bench.DEFAULT_WORKLOAD)
+g, proj, W, H, views = scn.g, scn.proj, scn.W, scn.H, scn.views
+views = [views[(k) % len(views)] for k in range(bench.ORBIT_VIEWS)]
 ref = B200Splatter(g, W, H, concurrent_frames=1, depth_slices=1)
-ref.updateProjection(proj); ref.updateFocalLengths(bench.FOV, bench.SCALE_DIV)
+ref.updateProjection(proj); ref.updateFocalLengths(bench.FOV, 1.0)
 want = []
 for v in views:
     ref.updateModelView(v); ref.execute()
     want.append((zlib.crc32(ref.getFrameBuffer().tobytes()), zlib.crc32(ref.getIPUHistogram().tobytes())))
 ref.close()
 s = B200Splatter(g, W, H)
-s.updateProjection(proj); s.updateFocalLengths(bench.FOV, bench.SCALE_DIV)
+s.updateProjection(proj); s.updateFocalLengths(bench.FOV, 1.0)
 depth, tickets, got, bad = 2 * s.concurrent_frames, [], 0, 0
 t0 = time.perf_counter()
 def take():

@@ -12,11 +12,12 @@ from gaussian_splat_ipu_b200.splatter import B200Splatter  # noqa: E402
 
 wl = sys.argv[1] if len(sys.argv) > 1 else bench.DEFAULT_WORKLOAD
 view = int(sys.argv[2]) if len(sys.argv) > 2 else 3
-g, base, proj, W, H = bench.make_scene(wl)
+scn = bench.make_scene(wl)
+g, proj, W, H, views = scn.g, scn.proj, scn.W, scn.H, scn.views
 s = B200Splatter(g, W, H, collect_timings=True)
-s.updateProjection(proj); s.updateFocalLengths(bench.FOV, bench.SCALE_DIV)
+s.updateProjection(proj); s.updateFocalLengths(bench.FOV, 1.0)
 for _ in range(3):
-    s.updateModelView(bench.view_for(base, view)); s.execute(sync=True)
+    s.updateModelView(views[(view) % len(views)]); s.execute(sync=True)
 print(wl, "view", view, "timings", {k: round(v, 4) for k, v in s.timings().items()})
 pairs, blended, cyc, prs = s.profile_tiles()
 cnt = s.getIPUHistogram().astype(np.int64)

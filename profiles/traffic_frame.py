@@ -8,22 +8,40 @@ out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], captu
 rows = list(csv.reader(io.StringIO(out)))
 hdr, units = rows[0], rows[1]
 ik, ir, iw, it = (hdr.index(k) for k in ("Kernel Name", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__time_duration.sum"))
+# hardware-side view of each kernel (bench.py copies the dominant stage's into roofline.ncu)
+PIPE = {"fma_pipe_pct": "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+        "fp64_pipe_pct": "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+        "issue_active_pct": "sm__issue_active.avg.pct_of_peak_sustained_active",
+        "threads_per_inst": "smsp__thread_inst_executed_per_inst_executed.ratio",
+        "warps_active_pct": "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "dram_throughput_pct": "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "tensor_pipe_pct": "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "registers": "launch__registers_per_thread"}
+ipipe = {k: hdr.index(v) for k, v in PIPE.items() if v in hdr}
 mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 tmult = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "usecond": 1.0, "nsecond": 1e-3, "msecond": 1e3}
 seq = []
 for r in rows[2:]:
     name = re.sub(r"\(.*", "", r[ik]).replace("void ", "").replace("gsplat::", "")
     b = float(r[ir].replace(",", "")) * mult[units[ir]] + float(r[iw].replace(",", "")) * mult[units[iw]]
-    seq.append((name, b, float(r[it].replace(",", "")) * tmult[units[it]]))
+    extra = {}
+    for k, i in ipipe.items():
+        try:
+            extra[k] = float(r[i].replace(",", ""))
+        except ValueError:
+            pass
+    seq.append((name, b, float(r[it].replace(",", "")) * tmult[units[it]], extra))
 starts = [i for i, s in enumerate(seq) if s[0].startswith("project_kernel")]
 a, b = starts[-2], starts[-1]          # the last complete frame of the capture
 frame = seq[a:b]
+
 STAGES = [("k1_project", r"project_kernel|tile_count|depth_quantile"), ("k3a_sort_depth", r"select_kernel|live_sat|rs_\w+<[7854]>"),
           ("k2_duplicate", r"duplicate_kernel"), ("k3b_sort_tile", r"rs_\w+<6>"), ("k4_ranges", r"tile_ranges"),
           ("k5_blend", r"blend_kernel|tile_order"), ("post_bgr8", r"bgr8")]
 # rs_scan_kernel carries no digit width: it belongs to the sort whose kernels surround it
 kern, stages, last_sort = {}, {}, "k3a_sort_depth"
-for name, by, us in frame:
+pipes_acc = {}
+for name, by, us, extra in frame:
     k = kern.setdefault(name, {"launches": 0, "dram_bytes": 0.0, "us": 0.0})
     k["launches"] += 1; k["dram_bytes"] += by; k["us"] += us
     st = next((s for s, pat in STAGES if re.search(pat, name)), None)
@@ -35,4 +53,9 @@ for name, by, us in frame:
         last_sort = st
     s = stages.setdefault(st or "other", {"launches": 0, "dram_bytes": 0.0, "us": 0.0})
     s["launches"] += 1; s["dram_bytes"] += by; s["us"] += us
-print(json.dumps({"source": sys.argv[1], "frame_launches": len(frame), "stages": stages, "kernels": kern}, indent=1))
+    pa = pipes_acc.setdefault(st or "other", {})       # duration-weighted mean of each metric over the stage's launches
+    for k, v in extra.items():
+        acc = pa.setdefault(k, [0.0, 0.0])
+        acc[0] += v * us; acc[1] += us
+pipes = {st: {k: round(a / w, 2) for k, (a, w) in d.items() if w > 0} for st, d in pipes_acc.items()}
+print(json.dumps({"source": sys.argv[1], "frame_launches": len(frame), "stages": stages, "pipes": pipes, "kernels": kern}, indent=1))

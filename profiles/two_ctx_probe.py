@@ -6,12 +6,13 @@ sys.path.insert(0, '.')
 import numpy as np, bench
 from gaussian_splat_ipu_b200.splatter import B200Splatter
 wl = sys.argv[1] if len(sys.argv) > 1 else bench.DEFAULT_WORKLOAD
-g, base, proj, W, H = bench.make_scene(wl)
-views = [bench.view_for(base, k) for k in range(bench.ORBIT_VIEWS)]
+scn = bench.make_scene(wl)
+g, proj, W, H, views = scn.g, scn.proj, scn.W, scn.H, scn.views
+views = [views[(k) % len(views)] for k in range(bench.ORBIT_VIEWS)]
 for nctx in ([int(sys.argv[2])] if len(sys.argv) > 2 else [1, 2, 3]):
     ss = [B200Splatter(g, W, H) for _ in range(nctx)]
     for s in ss:
-        s.updateProjection(proj); s.updateFocalLengths(bench.FOV, bench.SCALE_DIV)
+        s.updateProjection(proj); s.updateFocalLengths(bench.FOV, 1.0)
     def run(K):
         for k in range(K):
             s = ss[k % nctx]; s.updateModelView(views[k % 64]); s.execute()
