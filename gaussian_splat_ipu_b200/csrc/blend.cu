@@ -43,10 +43,10 @@ unsigned long long g_launches = 0;
 constexpr float ALPHA_MIN = 1.0f / 255.0f;
 
 #ifndef GSPLAT_BLEND_STAGES
-#define GSPLAT_BLEND_STAGES 4
+#define GSPLAT_BLEND_STAGES 3
 #endif
 #ifndef GSPLAT_BLEND_BATCH
-#define GSPLAT_BLEND_BATCH 64
+#define GSPLAT_BLEND_BATCH 128
 #endif
 constexpr int BLEND_STAGES = GSPLAT_BLEND_STAGES;    // ring depth
 constexpr int BLEND_BATCH = GSPLAT_BLEND_BATCH;      // list entries per ring stage (multiple of 32)
@@ -75,6 +75,7 @@ struct BlendSmem {
   unsigned long long empty[BLEND_STAGES];            // mbarrier: every consumer warp is done with the stage
   unsigned long long exp_tab[32];                    // exp_ref's 2^(k/32) table
   uint32_t warps_done;                               // consumer warps whose 32 pixels have all stopped
+  uint32_t strip_done[4];                            // the same per 8-pixel column strip of the part
   uint32_t stop;                                     // producer: nothing more will be staged
 };
 
@@ -89,17 +90,21 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long *bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
 }
+// Blocks until the phase of `bar` with the given parity has completed.  try_wait suspends the thread
+// in hardware for up to the time hint (ns) and returns early when the phase completes, so the long
+// hint costs no latency; without it the loop re-issues every few hundred cycles and a CTA's idle
+// producer warp alone burned 12 % of K5's issue slots spinning (profiles/prof_blend_r2a.txt).
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
       "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
       "@p bra DONE_%=;\n"
       "bra WAIT_%=;\n"
       "DONE_%=:\n"
       "}\n" ::"r"(smem_addr(bar)),
-      "r"(parity)
+      "r"(parity), "r"(0x989680u)
       : "memory");
 }
 // 48-byte global -> shared bulk copy, completion signalled on `bar` in bytes (complete_tx)
@@ -132,7 +137,9 @@ __device__ __forceinline__ bool blend_exact(const float4 b, const float4 c, floa
                                             float &Cb, float &Ca, unsigned long long &n_blend) {
   const float power = -0.5f * (b.x * dx * dx + b.z * dy * dy) - b.y * dx * dy;
   if (power > 0.0f) return false;
-  const float e = c.x * exp_ref(power, exp_tab);
+  // survivors of the pre-test have -13 < power <= 0: exp_ref's NaN / overflow / underflow branches
+  // cannot be taken and are skipped
+  const float e = c.x * exp_ref_core(power, exp_tab);
   const float alpha = e < 0.99f ? e : 0.99f;        // glm::min(0.99f, e)
   if (alpha < ALPHA_MIN) return false;
   const float test_T = T * (1.f - alpha);
@@ -173,12 +180,22 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   const uint32_t tile = order[blockIdx.x / nsub] + (uint32_t)row_begin * tiles_across;
   const uint2 range = ranges[tile];
   const uint32_t n = range.y - range.x;
-  const uint32_t part = tile * nsub + sub;
-  if (!FIRST && (n == 0 || ts.part_done[part])) return;   // nothing new for this part: its state stands
+  // "done" flags are kept per 8-pixel column STRIP of the tile (4 per tile) so that slices may cut
+  // the tile into different numbers of parts (the later, emptier slices use narrower parts)
+  const uint32_t strips = (uint32_t)part_w / 8u, strip0 = tile * 4u + sub * strips;
+  if (!FIRST) {
+    bool all_done = n == 0;                               // nothing new for this part: its state stands
+    if (!all_done) {
+      all_done = true;
+      for (uint32_t k = 0; k < strips; ++k) all_done = all_done && ts.part_done[strip0 + k];
+    }
+    if (all_done) return;
+  }
 
   if (tid == 0) {
     for (int s = 0; s < BLEND_STAGES; ++s) { mbar_init(&sm.full[s], BLEND_FULL_ARRIVALS); mbar_init(&sm.empty[s], NW); }
     sm.warps_done = 0;
+    sm.strip_done[0] = sm.strip_done[1] = sm.strip_done[2] = sm.strip_done[3] = 0;
     sm.stop = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -189,7 +206,16 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   const uint32_t tcol = tile % tiles_across, trow = tile / tiles_across;
 
   if (warp == NW) {
-    // ---- producer: the tile's list, BLEND_BATCH entries per stage, one bulk copy per entry -------
+    // ---- producer: the tile's list, BLEND_BATCH entries per stage --------------------------------
+    // The list indices of stage it + 1 are loaded while the producer waits for stage it's slot, so a
+    // stage costs the producer one round trip (the record copies, asynchronous), not two.
+    constexpr uint32_t PER_LANE = BLEND_BATCH / 32;
+    uint32_t gidx[PER_LANE];
+#pragma unroll
+    for (uint32_t q = 0; q < PER_LANE; ++q) {
+      const uint32_t j = q * 32 + lane;
+      gidx[q] = j < n ? __ldg(&vals[range.x + j]) : 0u;
+    }
     for (uint32_t it = 0; it < nbatch; ++it) {
       const uint32_t stage = it % BLEND_STAGES, use = it / BLEND_STAGES;
       mbar_wait(&sm.empty[stage], (use & 1u) ^ 1u);        // first use of a stage: passes at once
@@ -205,10 +231,10 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       __syncwarp();
 #endif
 #pragma unroll
-      for (uint32_t j = lane; j < (uint32_t)BLEND_BATCH; j += 32) {
+      for (uint32_t q = 0; q < PER_LANE; ++q) {
+        const uint32_t j = q * 32 + lane;
         if (j < cnt) {
-          const uint32_t g = __ldg(&vals[range.x + base + j]);
-          const float4 *src = p.rec + (size_t)g * 3;
+          const float4 *src = p.rec + (size_t)gidx[q] * 3;
           float4 *dst = &sm.ring[stage][j * 3];
 #if GSPLAT_BLEND_TMA
           bulk_copy_48(dst, src, &sm.full[stage]);
@@ -220,6 +246,11 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
 #if !GSPLAT_BLEND_TMA
       async_copies_arrive(&sm.full[stage]);   // every lane: one of the 32 arrivals, once its copies have landed
 #endif
+#pragma unroll
+      for (uint32_t q = 0; q < PER_LANE; ++q) {            // next stage's indices
+        const uint32_t j = base + BLEND_BATCH + q * 32 + lane;
+        gidx[q] = j < n ? __ldg(&vals[range.x + j]) : 0u;
+      }
     }
   } else {
     // ---- consumers ---------------------------------------------------------------------------
@@ -246,7 +277,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
     uint32_t stop_at = done ? 0u : n;   // COUNT: list entries this pixel visits (reference semantics)
     unsigned long long n_blend = 0;     // COUNT
     bool warp_done = __all_sync(0xffffffffu, done);
-    if (warp_done && lane == 0) atomicAdd(&sm.warps_done, 1u);
+    if (warp_done && lane == 0) { atomicAdd(&sm.strip_done[cb], 1u); atomicAdd(&sm.warps_done, 1u); }
 
     for (uint32_t it = 0; it < nbatch; ++it) {
       const uint32_t stage = it % BLEND_STAGES, use = it / BLEND_STAGES;
@@ -331,7 +362,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
 #endif
           if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
         }
-        if (warp_done && lane == 0) atomicAdd(&sm.warps_done, 1u);   // before the release below
+        if (warp_done && lane == 0) { atomicAdd(&sm.strip_done[cb], 1u); atomicAdd(&sm.warps_done, 1u); }   // before the release below
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.empty[stage]);
@@ -354,10 +385,11 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
     if (valid) fb[px] = make_float4(Cr, Cg, Cb, Ca);
   }
   if (!LAST) {
-    __syncthreads();   // every consumer warp has added itself to warps_done if its pixels have stopped
-    if (tid == 0 && sm.warps_done == NW) {
-      ts.part_done[part] = 1;
-      if (atomicAdd(&ts.parts_done[tile], 1u) + 1u == nsub) ts.tile_done[tile] = 1;   // last part of the tile to stop
+    __syncthreads();   // every consumer warp has added itself to the counters if its pixels have stopped
+    const uint32_t row_blocks = NW / strips;
+    if (tid < strips && sm.strip_done[tid] == row_blocks && !ts.part_done[strip0 + tid]) {
+      ts.part_done[strip0 + tid] = 1;
+      if (atomicAdd(&ts.parts_done[tile], 1u) + 1u == 4u) ts.tile_done[tile] = 1;   // last strip of the tile to stop
     }
   }
 }

@@ -140,7 +140,8 @@ struct gsplat_ctx {
   uint2 *ranges_last = nullptr;    // ranges of the last slice of the last frame
   uint8_t *tile_state = nullptr;   // inside frame_block: TileState arrays
   TileState ts{};                  // per tile / per part: every pixel has stopped
-  int blend_split = 1;             // K5 CTAs per semantic tile
+  int blend_split = 1;             // K5 CTAs per semantic tile in the first depth slice
+  int blend_split_later = 1;       // ... and in the later slices (fewer live tiles: narrower parts fill the SMs)
   // frame graphs: [0] one slice, [1] sliced; dropped whenever buffers, scene or band change
   FrameGraph graphs[2];
   bool use_graphs = true;          // GSPLAT_GRAPHS=0 disables (eager launches)
@@ -511,6 +512,10 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     if (const char *e = std::getenv("GSPLAT_K5_SPLIT")) split = std::atoi(e);
     if (split != 1 && split != 2 && split != 4) split = 2;
     ctx->blend_split = split;
+    int later = 4;
+    if (const char *e = std::getenv("GSPLAT_K5_SPLIT_LATER")) later = std::atoi(e);
+    if (later != 1 && later != 2 && later != 4) later = 4;
+    ctx->blend_split_later = later;
     if (const char *e = std::getenv("GSPLAT_GRAPHS")) ctx->use_graphs = std::atoi(e) != 0;
     CUC(cudaMalloc(&ctx->tstate, sizeof(float) * px));
   }

@@ -113,13 +113,23 @@ __device__ __forceinline__ unsigned long long lb_exclusive_prefix(unsigned long 
 
 #ifdef __CUDACC__
 // expf as the host libm computes it.  The reference's codelets call exp() on floats
-// (ipu_geometry.hpp:319-321); host-compiled, that is glibc's expf (sysdeps/ieee754/flt-32/e_expf.c,
-// glibc >= 2.27; the algorithm of ARM's optimized-routines): with N = 32,
+// (ipu_geometry.hpp:319-321, codelets.cpp:400); host-compiled, that is glibc's expf
+// (sysdeps/ieee754/flt-32/e_expf.c, glibc >= 2.27; the algorithm of ARM's optimized-routines):
+// with N = 32,
 //   k = round(x * N / ln2),  r = x * N / ln2 - k,  exp(x) = 2^(k/N) * P(r),
 // 2^(k/N) from a 32-entry table of doubles (exponent bits added by integer arithmetic), P a cubic,
 // all in f64, rounded once to f32.  Restated here with the same table, constants and operation
 // order, so the result is bit-identical to the oracle's (a correctly rounded exp differs from it
 // for about one argument in 2000) at a fraction of the f64 work of exp(double).
+// On x86-64 glibc dispatches expf through an ifunc: CPUs with FMA + AVX2 (every host this runs
+// beside) get __expf_fma, the same source compiled with contraction — five of its products are
+// fused into the following add (disassembly of libm 2.39: vfmadd132sd for z + SHIFT, vfmsub132sd
+// for r, vfmadd213sd / vfmadd132sd x 2 for the polynomial).  GSPLAT_EXPF_FMA = 1 (default) restates
+// that variant (8 f64 operations), 0 the unfused one (12).  Both agree with the host's expf on every
+// one of 3e8 (CPU) / 6.7e7 (GPU, profiles/micro/exp_check.cu) sampled arguments in [-16, 0.8].
+#ifndef GSPLAT_EXPF_FMA
+#define GSPLAT_EXPF_FMA 1
+#endif
 static __constant__ unsigned long long EXPF_TAB[32] = {
     0x3ff0000000000000ull, 0x3fefd9b0d3158574ull, 0x3fefb5586cf9890full, 0x3fef9301d0125b51ull,
     0x3fef72b83c7d517bull, 0x3fef54873168b9aaull, 0x3fef387a6e756238ull, 0x3fef1e9df51fdee1ull,
@@ -130,25 +140,41 @@ static __constant__ unsigned long long EXPF_TAB[32] = {
     0x3feee89f995ad3adull, 0x3feeff76f2fb5e47ull, 0x3fef199bdd85529cull, 0x3fef3720dcef9069ull,
     0x3fef5818dcfba487ull, 0x3fef7c97337b9b5full, 0x3fefa4afa2a490daull, 0x3fefd0765b6e4540ull,
 };
+// the main path of expf: valid for -103.97 < x < 88.72 (no NaN / overflow / underflow handling)
+__device__ __forceinline__ float exp_ref_core(float x, const unsigned long long *tab /* EXPF_TAB in shared memory */) {
+  constexpr double INVLN2N = 0x1.71547652b82fep+0 * 32.0, SHIFT = 0x1.8p+52;
+  constexpr double C0 = 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0, C1 = 0x1.ebfce50fac4f3p-3 / 32.0 / 32.0,
+                   C2 = 0x1.62e42ff0c52d6p-1 / 32.0;
+  const double xd = (double)x;
+#if GSPLAT_EXPF_FMA
+  double kd = __fma_rn(INVLN2N, xd, SHIFT);
+  const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+  kd = __dsub_rn(kd, SHIFT);
+  const double r = __fma_rn(INVLN2N, xd, -kd);
+  const double s = __longlong_as_double((long long)(tab[ki & 31ull] + (ki << 47)));
+  const double zz = __fma_rn(C0, r, C1), r2 = __dmul_rn(r, r);
+  double y = __fma_rn(C2, r, 1.0);
+  y = __fma_rn(zz, r2, y);
+  return (float)__dmul_rn(y, s);
+#else
+  const double z = __dmul_rn(INVLN2N, xd);
+  double kd = __dadd_rn(z, SHIFT);
+  const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+  kd = __dsub_rn(kd, SHIFT);
+  const double r = __dsub_rn(z, kd);
+  const double s = __longlong_as_double((long long)(tab[ki & 31ull] + (ki << 47)));
+  const double zz = __dadd_rn(__dmul_rn(C0, r), C1), r2 = __dmul_rn(r, r);
+  double y = __dadd_rn(__dmul_rn(C2, r), 1.0);
+  y = __dadd_rn(__dmul_rn(zz, r2), y);
+  return (float)__dmul_rn(y, s);
+#endif
+}
 __device__ __forceinline__ float exp_ref(float x, const unsigned long long *tab /* EXPF_TAB in shared memory */) {
   if (!(x == x)) return x + x;
   if (x > 88.72283172607421875f) return __int_as_float(0x7f800000);    // 0x1.62e42ep6f: overflow
   if (x < -103.97207641601562500f) return 0.0f;                        // -0x1.9fe368p6f: underflow
-  constexpr double INVLN2N = 0x1.71547652b82fep+0 * 32.0, SHIFT = 0x1.8p+52;
-  constexpr double C0 = 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0, C1 = 0x1.ebfce50fac4f3p-3 / 32.0 / 32.0,
-                   C2 = 0x1.62e42ff0c52d6p-1 / 32.0;
-  const double z = INVLN2N * (double)x;
-  double kd = z + SHIFT;
-  const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
-  kd -= SHIFT;
-  const double r = z - kd;
-  const double s = __longlong_as_double((long long)(tab[ki & 31ull] + (ki << 47)));
-  const double zz = C0 * r + C1, r2 = r * r;
-  double y = C2 * r + 1.0;
-  y = zz * r2 + y;
-  return (float)(y * s);
+  return exp_ref_core(x, tab);
 }
-
 #endif
 
 constexpr uint32_t DEPTH_KEY_CULLED = 0xffffffffu;
@@ -270,8 +296,8 @@ void launch_tile_ranges(const uint32_t *keys, const uint32_t *d_n, uint32_t n_up
 // first, and K5 takes its tiles in that order.
 struct TileState {
   uint8_t *tile_done;    // [tiles] every pixel of the tile has stopped (read by K2 of later slices)
-  uint8_t *part_done;    // [tiles * BLEND_MAX_SPLIT] every pixel of the part has stopped
-  uint32_t *parts_done;  // [tiles] parts of the tile that have stopped
+  uint8_t *part_done;    // [tiles * 4 (of BLEND_MAX_SPLIT slots)] every pixel of the tile's 8-column strip has stopped
+  uint32_t *parts_done;  // [tiles] strips of the tile that have stopped (4 = the whole tile)
 };
 constexpr int BLEND_MAX_SPLIT = 8;
 inline size_t tile_state_bytes(int tiles) { return (size_t)tiles * (1 + BLEND_MAX_SPLIT + 4) + 16; }

@@ -16,7 +16,7 @@ __global__ void k(const float *x, float *y, int n) {
   if (i < n) y[i] = exp_ref(x[i], tab);
 }
 int main() {
-  const int N = 1 << 26;
+  const int N = 1 << 28;
   std::vector<float> x(N), y(N);
   uint64_t st = 88172645463325252ull;
   for (int i = 0; i < N; ++i) {
