@@ -162,7 +162,7 @@ __device__ __forceinline__ bool blend_exact(const float4 b, const float4 c, floa
 template <bool COUNT, bool FIRST, bool LAST>
 __global__ void __launch_bounds__((BLEND_MAX_WARPS + 1) * 32)
 blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
-             int tiles_across, int row_begin, int full_tile_h, int part_w, float4 *__restrict__ fb,
+             int tiles_across, const uint32_t *__restrict__ band, int full_tile_h, int part_w, float4 *__restrict__ fb,
              float *__restrict__ tstate, TileState ts, const uint32_t *__restrict__ order,
              unsigned long long *__restrict__ pair_counters) {
   extern __shared__ __align__(128) unsigned char blend_smem_raw[];
@@ -176,8 +176,11 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   // a few pixels across then occupies a third of the lanes of the warps it reaches, where a
   // 32 x 1 pixel row would leave nine lanes in ten idle.
   const uint32_t nsub = (uint32_t)(32 / part_w), sub = blockIdx.x % nsub;
+  // the grid covers the whole image; this context's band (device words written by K1) may be less
+  const uint32_t row_begin = band[0], row_end = band[1];
+  if (blockIdx.x / nsub >= (row_end - row_begin) * (uint32_t)tiles_across) return;
   // tiles are taken longest list first (tile_order_kernel) so the long ones do not start last
-  const uint32_t tile = order[blockIdx.x / nsub] + (uint32_t)row_begin * tiles_across;
+  const uint32_t tile = order[blockIdx.x / nsub] + row_begin * (uint32_t)tiles_across;
   const uint2 range = ranges[tile];
   const uint32_t n = range.y - range.x;
   // "done" flags are kept per 8-pixel column STRIP of the tile (4 per tile) so that slices may cut
@@ -408,9 +411,11 @@ __device__ __forceinline__ uint32_t order_bucket(uint32_t len) {
   return (31u - e) * 4u + (3u - m);                                     // longer lists -> smaller bucket
 }
 __global__ void __launch_bounds__(1024)
-tile_order_kernel(const uint2 *__restrict__ ranges, int tiles_across, int row_begin, int ntiles,
+tile_order_kernel(const uint2 *__restrict__ ranges, int tiles_across, const uint32_t *__restrict__ band,
                   const uint8_t *__restrict__ tile_done, uint32_t *__restrict__ order) {
   __shared__ uint32_t cnt[ORDER_BUCKETS];
+  const uint32_t row_begin = band[0];
+  const int ntiles = (int)((band[1] - row_begin) * (uint32_t)tiles_across);
   for (int k = threadIdx.x; k < ORDER_BUCKETS; k += blockDim.x) cnt[k] = 0;
   __syncthreads();
   const uint32_t t0 = (uint32_t)row_begin * tiles_across;
@@ -451,26 +456,23 @@ tile_order_kernel(const uint2 *__restrict__ ranges, int tiles_across, int row_be
   }
 }
 
-static void launch_tile_order(const uint2 *ranges, const FrameParams &fp, const uint8_t *tile_done, bool first,
-                              uint32_t *order, cudaStream_t st) {
-  const int ntiles = (fp.row_end - fp.row_begin) * fp.tiles_across;
-  if (ntiles <= 0) return;
+static void launch_tile_order(const uint2 *ranges, const FrameParams &fp, const uint32_t *band, const uint8_t *tile_done,
+                              bool first, uint32_t *order, cudaStream_t st) {
   ++g_launches;
-  tile_order_kernel<<<1, 1024, 0, st>>>(ranges, fp.tiles_across, fp.row_begin, ntiles, first ? nullptr : tile_done, order);
+  tile_order_kernel<<<1, 1024, 0, st>>>(ranges, fp.tiles_across, band, first ? nullptr : tile_done, order);
 }
 
 template <bool COUNT, bool FIRST, bool LAST>
 static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                           float4 *fb_tiled, float *tstate, const TileState &ts, int split, const uint32_t *order,
-                           unsigned long long *pair_counters, cudaStream_t st) {
-  const int rows = fp.row_end - fp.row_begin;
-  if (rows <= 0) return;
+                           const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split,
+                           const uint32_t *order, unsigned long long *pair_counters, cudaStream_t st) {
+  const int rows = fp.tiles_down;   // launch geometry for the whole image: the band is only known on the device
   const int full_h = (int)fp.tile_h;
   const int part_w = 32 / split;                                  // columns per CTA (split is 1, 2 or 4)
   const int warps = (part_w / 8) * ((full_h + 3) / 4);           // one consumer warp per 8 x 4 pixel block
   ++g_launches;
   blend_kernel<COUNT, FIRST, LAST><<<rows * fp.tiles_across * split, (warps + 1) * 32, sizeof(BlendSmem), st>>>(
-      p, sorted_vals, ranges, fp.tiles_across, fp.row_begin, full_h, part_w, fb_tiled, tstate, ts, order, pair_counters);
+      p, sorted_vals, ranges, fp.tiles_across, band, full_h, part_w, fb_tiled, tstate, ts, order, pair_counters);
 }
 
 template <bool COUNT, bool FIRST, bool LAST> static cudaError_t blend_attr() {
@@ -490,10 +492,10 @@ cudaError_t setup_blend_kernels() {
 }
 
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                  float4 *fb_tiled, float *tstate, const TileState &ts, int split, uint32_t *order, bool first,
-                  bool last, unsigned long long *pair_counters, cudaStream_t st) {
-  launch_tile_order(ranges, fp, ts.tile_done, first, order, st);
-#define GSPLAT_BLEND(C, F, L) launch_blend_t<C, F, L>(p, sorted_vals, ranges, fp, fb_tiled, tstate, ts, split, order, pair_counters, st)
+                  const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split, uint32_t *order,
+                  bool first, bool last, unsigned long long *pair_counters, cudaStream_t st) {
+  launch_tile_order(ranges, fp, band, ts.tile_done, first, order, st);
+#define GSPLAT_BLEND(C, F, L) launch_blend_t<C, F, L>(p, sorted_vals, ranges, fp, band, fb_tiled, tstate, ts, split, order, pair_counters, st)
   if (pair_counters) {
     if (first) { if (last) GSPLAT_BLEND(true, true, true); else GSPLAT_BLEND(true, true, false); }
     else { if (last) GSPLAT_BLEND(true, false, true); else GSPLAT_BLEND(true, false, false); }
@@ -516,12 +518,12 @@ __device__ __forceinline__ uint32_t to_u8(float v) {
 }
 
 __global__ void __launch_bounds__(256)
-bgr8_kernel(const float4 *__restrict__ fb, uint8_t *__restrict__ bgr, int W, int H, int tile_w, int tile_h,
+bgr8_kernel(const float4 *__restrict__ fb, uint8_t *__restrict__ bgr, int W, int y0, int y1, int tile_w, int tile_h,
             int tiles_across) {
   const int quads_per_row = W / 4;
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= quads_per_row * H) return;
-  const int y = q / quads_per_row, x = (q % quads_per_row) * 4;
+  if (q >= quads_per_row * (y1 - y0)) return;
+  const int y = y0 + q / quads_per_row, x = (q % quads_per_row) * 4;
   const int tile = (y / tile_h) * tiles_across + x / tile_w;
   const float4 *src = fb + (size_t)tile * (tile_w * tile_h) + (y % tile_h) * tile_w + (x % tile_w);
   uint32_t b[12];
@@ -537,9 +539,16 @@ bgr8_kernel(const float4 *__restrict__ fb, uint8_t *__restrict__ bgr, int W, int
 }
 
 void launch_bgr8(const float4 *fb_tiled, uint8_t *bgr, int W, int H, int tile_w, int tile_h, cudaStream_t st) {
-  const int quads = (W / 4) * H;
+  launch_bgr8_rows(fb_tiled, bgr, W, 0, H, tile_w, tile_h, st);
+}
+
+// image rows [y0, y1) only (a tile-row band of a multi-GPU frame); `bgr` is the whole image
+void launch_bgr8_rows(const float4 *fb_tiled, uint8_t *bgr, int W, int y0, int y1, int tile_w, int tile_h,
+                      cudaStream_t st) {
+  const int quads = (W / 4) * (y1 - y0);
+  if (quads <= 0) return;
   ++g_launches;
-  bgr8_kernel<<<ceil_div(quads, 256), 256, 0, st>>>(fb_tiled, bgr, W, H, tile_w, tile_h, W / tile_w);
+  bgr8_kernel<<<ceil_div(quads, 256), 256, 0, st>>>(fb_tiled, bgr, W, y0, y1, tile_w, tile_h, W / tile_w);
 }
 
 }  // namespace gsplat

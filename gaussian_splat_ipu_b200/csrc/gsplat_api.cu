@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -56,11 +57,13 @@ struct StreamSlot {
 // device scalars
 // device scalars; words [0, SC_FRAME_WORDS) are zeroed at the start of every frame and copied to
 // the frame slot's pinned words at its end
-enum Scalar { SC_V = 0, SC_OVERFLOW = 1, SC_TICKET0 = 8 /* K2 chain ticket per slice */,
+enum Scalar { SC_V = 0, SC_OVERFLOW = 1, SC_BAND0 = 2 /* = SC_V + BAND_WORD_OFFSET: {row_begin, row_end}, written by K1 */,
+              SC_TICKET0 = 8 /* K2 chain ticket per slice */,
               SC_DS0 = 16 /* duplicates emitted per slice */, SC_NS0 = 24 /* Gaussians selected per slice */,
               SC_SELTICKET0 = 32 /* selection chain ticket per slice */, SC_TAU0 = 40 /* depth-key thresholds */,
               SC_KRANGE0 = 48 /* {max, max of ~} depth key of each slice's selection (2 words per slice) */,
               SC_FRAME_WORDS = 64 };
+static_assert(SC_BAND0 == SC_V + gsplat::BAND_WORD_OFFSET, "K1 writes the band next to its drawn counter");
 enum Persist { P_N = 0 /* scene size */, P_SORT_N = 1 /* gsplat_sort_pairs count */, P_COUNT = 16 };
 
 // A captured frame (CUDA graph): the whole stage sequence of one frame for one slicing mode.  Only
@@ -642,22 +645,23 @@ int gsplat_set_band(gsplat_ctx *ctx, int row_begin, int row_end) {
   if (!ctx) return GSPLAT_E_ARG;
   if (row_begin < 0 || row_end > ctx->tiles_down || row_begin > row_end)
     return fail(ctx, GSPLAT_E_ARG, "gsplat_set_band: bad tile-row band");
-  if (row_begin != ctx->cfg.band_row_begin || row_end != ctx->cfg.band_row_end) {
-    cudaSetDevice(ctx->cfg.device);
-    cudaStreamSynchronize(ctx->st);   // captured frames of the old band may still be running
-    drop_graphs(ctx);
-  }
+  // no re-capture: the band reaches the frame through K1's argument block (refreshed per frame) and
+  // from there, on the device, the kernels behind it
+  const bool changed = row_begin != ctx->cfg.band_row_begin || row_end != ctx->cfg.band_row_end;
   ctx->cfg.band_row_begin = row_begin;
   ctx->cfg.band_row_end = row_end;
   ctx->fp.row_begin = row_begin;
   ctx->fp.row_end = row_end;
-  // tiles that leave the band must read count 0 until the next frame's tile_count_finish_kernel
-  // rewrites every count (rectangles are clamped to the band in K1, so outside tiles count 0)
-  CU(cudaSetDevice(ctx->cfg.device));
-  CU(cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * ctx->num_tiles, ctx->st));
+  if (changed) {
+    // tiles that leave the band must read count 0 until the next frame's tile_count_finish_kernel
+    // rewrites every count (rectangles are clamped to the band in K1, so outside tiles count 0)
+    CU(cudaSetDevice(ctx->cfg.device));
+    CU(cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * ctx->num_tiles, ctx->st));
+  }
   return GSPLAT_OK;
 }
 
 }  // extern "C"
 
 #include "gsplat_api_frame.inc"
+#include "gsplat_group.inc"

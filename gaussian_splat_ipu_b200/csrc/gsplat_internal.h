@@ -181,6 +181,9 @@ constexpr uint32_t DEPTH_KEY_CULLED = 0xffffffffu;
 constexpr uint32_t RECT_EMPTY = 1u;   // {lo = 1, hi = 0}: the rectangle of a Gaussian that is not drawn
 
 constexpr int K1_THREADS = 256;
+// K1 (and the parity inject) write the frame's band {row_begin, row_end} at this word offset from
+// their drawn counter; tile_order and K5 read it there (`band` arguments below)
+constexpr int BAND_WORD_OFFSET = 2;
 
 // ---- launchers (all asynchronous on `st`) ------------------------------------------------
 void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st);
@@ -301,13 +304,17 @@ struct TileState {
 };
 constexpr int BLEND_MAX_SPLIT = 8;
 inline size_t tile_state_bytes(int tiles) { return (size_t)tiles * (1 + BLEND_MAX_SPLIT + 4) + 16; }
+// `band`: device words {row_begin, row_end} of the frame's tile-row band (written by K1); the grid
+// covers every tile of the image and the CTAs beyond the band leave at once.
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                  float4 *fb_tiled, float *tstate, const TileState &ts, int split, uint32_t *order, bool first,
-                  bool last, unsigned long long *pair_counters, cudaStream_t st);
+                  const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split, uint32_t *order,
+                  bool first, bool last, unsigned long long *pair_counters, cudaStream_t st);
 
 // a10: tiled f32 RGBA -> de-tiled BGR8 rows.
 void launch_bgr8(const float4 *fb_tiled, uint8_t *bgr, int W, int H, int tile_w, int tile_h,
                  cudaStream_t st);
+void launch_bgr8_rows(const float4 *fb_tiled, uint8_t *bgr, int W, int y0, int y1, int tile_w, int tile_h,
+                      cudaStream_t st);
 
 // cudaFuncAttributeMaxDynamicSharedMemorySize is a property of (kernel, device context): every
 // device a context is created on needs its own opt-in.  gsplat_create calls these once per device

@@ -64,6 +64,13 @@ __device__ __forceinline__ uint32_t clamp_rect(int &c0, int &c1, int &r0, int &r
 __global__ void __launch_bounds__(K1_THREADS)
 project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__ drawn_counter,
                float *__restrict__ dbg_rec8, int32_t *__restrict__ dbg_rect4) {
+  // the frame's tile-row band, for the kernels behind K1 in the (captured) frame: only K1's
+  // argument block is refreshed per frame, so a band change needs no re-capture (drawn_counter is
+  // word SC_V of the frame scalars; the band words sit at BAND_WORD_OFFSET from it)
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    drawn_counter[BAND_WORD_OFFSET] = (uint32_t)fp.row_begin;
+    drawn_counter[BAND_WORD_OFFSET + 1] = (uint32_t)fp.row_end;
+  }
   __shared__ uint32_t red[K1_THREADS / 32];
   // the exp table is indexed per thread: from constant memory every distinct index of a warp is a
   // separate replay, from shared memory it is one (at worst two-way conflicted) access
@@ -228,6 +235,10 @@ inject_kernel(const float *__restrict__ depth, const int32_t *__restrict__ rect4
               const uint8_t *__restrict__ drawn, uint32_t n, FrameParams fp, Projected out,
               uint32_t *__restrict__ drawn_counter) {
   __shared__ uint32_t red[K1_THREADS / 32];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {   // as K1: publish the band
+    drawn_counter[BAND_WORD_OFFSET] = (uint32_t)fp.row_begin;
+    drawn_counter[BAND_WORD_OFFSET + 1] = (uint32_t)fp.row_end;
+  }
   const uint32_t i = blockIdx.x * K1_THREADS + threadIdx.x;
   uint32_t touched = 0;
   if (i < n) {
@@ -272,17 +283,15 @@ const void *project_kernel_address() { return reinterpret_cast<const void *>(&pr
 
 void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *drawn_counter,
                     float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st) {
-  if (!scene.n) return;
-  ++g_launches;
-  project_kernel<<<ceil_div(scene.n, K1_THREADS), K1_THREADS, 0, st>>>(scene, fp, out, drawn_counter, dbg_rec8,
+  ++g_launches;   // an empty scene still launches one CTA: K1 publishes the frame's band
+  project_kernel<<<scene.n ? ceil_div(scene.n, K1_THREADS) : 1, K1_THREADS, 0, st>>>(scene, fp, out, drawn_counter, dbg_rec8,
                                                                       dbg_rect4);
 }
 
 void launch_inject(const float *depth, const int32_t *rect4, const uint8_t *drawn, uint32_t n,
                    const FrameParams &fp, Projected out, uint32_t *drawn_counter, cudaStream_t st) {
-  if (!n) return;
   ++g_launches;
-  inject_kernel<<<ceil_div(n, K1_THREADS), K1_THREADS, 0, st>>>(depth, rect4, drawn, n, fp, out, drawn_counter);
+  inject_kernel<<<n ? ceil_div(n, K1_THREADS) : 1, K1_THREADS, 0, st>>>(depth, rect4, drawn, n, fp, out, drawn_counter);
 }
 
 }  // namespace gsplat

@@ -79,6 +79,19 @@ SYMBOLS = {
     "gsplat_timer_end": (C.c_int, [_vp, _fp]),
     "gsplat_launch_count": (C.c_uint64, []),
     "gsplat_flush_l2": (C.c_int, [_vp]),
+    "gsplat_create_group": (C.c_int, [C.POINTER(Config), C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(_vp)]),
+    "gsplat_destroy_group": (None, [_vp]),
+    "gsplat_group_last_error": (C.c_char_p, [_vp]),
+    "gsplat_group_size": (C.c_int, [_vp]),
+    "gsplat_group_upload_scene": (C.c_int, [_vp, _fp, C.c_size_t]),
+    "gsplat_group_set_camera": (C.c_int, [_vp, _fp, _fp, C.c_float, C.c_float]),
+    "gsplat_group_render_streamed": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "gsplat_group_acquire_frame": (C.c_int, [_vp, C.c_uint64, C.POINTER(_vp), C.POINTER(_vp)]),
+    "gsplat_group_max_outstanding": (C.c_int, [_vp]),
+    "gsplat_group_sync": (C.c_int, [_vp]),
+    "gsplat_group_get_bands": (C.c_int, [_vp, C.POINTER(C.c_int), C.c_int]),
+    "gsplat_group_member": (_vp, [_vp, C.c_int]),
+    "gsplat_balance_bands": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "gsplat_concurrent_frames": (C.c_int, [_vp]),
     "gsplat_count_pairs": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
 }
@@ -357,3 +370,103 @@ class B200Splatter:
 
     def postprocess_bgr8(self):
         self._check(self.lib.gsplat_postprocess_bgr8(self.h))
+
+
+GROUP_VIEWS, GROUP_BANDS = 0, 1
+
+
+def balance_bands_native(tile_counts: np.ndarray, tiles_across: int, tiles_down: int, n_bands: int, tile_pixels: int = 640):
+    """The library's band balancer (gsplat_balance_bands; host only): n_bands + 1 tile-row cuts."""
+    lib = load_library()
+    c = np.ascontiguousarray(tile_counts, np.uint32)
+    cuts = (C.c_int * (n_bands + 1))()
+    rc = lib.gsplat_balance_bands(c.ctypes.data, tiles_across, tiles_down, tile_pixels, n_bands, cuts)
+    if rc:
+        raise GsplatError(rc, "gsplat_balance_bands")
+    return list(cuts)
+
+
+class B200Group:
+    """Several B200s of this process behind one IpuSplatter-shaped object (gsplat_create_group):
+    mode GROUP_VIEWS (whole frames to the devices in turn) or GROUP_BANDS (every frame cut into
+    tile-row bands, gathered on devices[0] over NCCL).  The reference drives one IPU
+    (src/main/splat.cpp:41-46); the surface mirrored here is the same updateModelView /
+    updateProjection / updateFocalLengths + the frame stream."""
+
+    def __init__(self, gaussians16, devices, mode=GROUP_BANDS, width=1280, height=720, tile_w=32, tile_h=20,
+                 depth_slices=0, concurrent_frames=0, dup_capacity=0):
+        self.lib = load_library()
+        cfg = Config()
+        self.lib.gsplat_config_default(C.byref(cfg))
+        cfg.width, cfg.height, cfg.tile_w, cfg.tile_h = width, height, tile_w, tile_h
+        cfg.depth_slices, cfg.concurrent_frames, cfg.dup_capacity = int(depth_slices), int(concurrent_frames), dup_capacity
+        devs = (C.c_int * len(devices))(*devices)
+        self.h = _vp()
+        rc = self.lib.gsplat_create_group(C.byref(cfg), devs, len(devices), int(mode), C.byref(self.h))
+        if rc:
+            self.h = _vp()
+            raise GsplatError(rc, self.lib.gsplat_group_last_error(None).decode())
+        self.mode, self.n = mode, len(devices)
+        self.width, self.height, self.tile_w, self.tile_h = width, height, tile_w, tile_h
+        self.tiles_across, self.tiles_down = width // tile_w, height // tile_h
+        self.num_tiles = self.tiles_across * self.tiles_down
+        self._mv = np.eye(4, dtype=np.float32)
+        self._proj = np.eye(4, dtype=np.float32)
+        self._fxy = (float(np.radians(np.float32(40.0))), 0.1)
+        self._slot_views = {}
+        g = np.ascontiguousarray(gaussians16, dtype=np.float32).reshape(-1, 16)
+        self._check(self.lib.gsplat_group_upload_scene(self.h, g.ctypes.data_as(_fp), g.shape[0]))
+
+    def _check(self, rc):
+        if rc < 0:
+            raise GsplatError(rc, self.lib.gsplat_group_last_error(self.h).decode())
+        return rc
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.lib.gsplat_destroy_group(self.h)
+            self.h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def updateModelView(self, mv):
+        self._mv = np.ascontiguousarray(mv, dtype=np.float32).reshape(4, 4)
+
+    def updateProjection(self, mp):
+        self._proj = np.ascontiguousarray(mp, dtype=np.float32).reshape(4, 4)
+
+    def updateFocalLengths(self, fx, fy):
+        self._fxy = (float(fx), float(fy))
+
+    @property
+    def max_outstanding(self) -> int:
+        return int(self.lib.gsplat_group_max_outstanding(self.h))
+
+    def bands(self):
+        cuts = (C.c_int * (self.n + 1))()
+        self._check(self.lib.gsplat_group_get_bands(self.h, cuts, self.n + 1))
+        return list(cuts)
+
+    def executeStreamed(self) -> int:
+        self._check(self.lib.gsplat_group_set_camera(self.h, self._mv.ctypes.data_as(_fp), self._proj.ctypes.data_as(_fp),
+                                                     self._fxy[0], self._fxy[1]))
+        t = C.c_uint64()
+        self._check(self.lib.gsplat_group_render_streamed(self.h, C.byref(t)))
+        return int(t.value)
+
+    def acquireFrame(self, ticket: int):
+        b, c = _vp(), _vp()
+        self._check(self.lib.gsplat_group_acquire_frame(self.h, ticket, C.byref(b), C.byref(c)))
+        views = self._slot_views.get(b.value)
+        if views is None:
+            img = np.frombuffer((C.c_uint8 * (self.height * self.width * 3)).from_address(b.value), np.uint8)
+            cnt = np.frombuffer((C.c_uint32 * self.num_tiles).from_address(c.value), np.uint32)
+            views = self._slot_views[b.value] = (img.reshape(self.height, self.width, 3), cnt)
+        return views
+
+    def sync(self):
+        self._check(self.lib.gsplat_group_sync(self.h))

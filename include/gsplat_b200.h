@@ -38,7 +38,8 @@ typedef enum gsplat_status {
   GSPLAT_E_CUDA = -2,     /* CUDA runtime error (message has the cudaError string)       */
   GSPLAT_E_CAPACITY = -3, /* duplicate buffer could not be grown (never a silent drop;   */
                           /* the reference drops silently, codelets.cpp:565-569)         */
-  GSPLAT_E_STATE = -4     /* e.g. render before upload_scene / set_camera                */
+  GSPLAT_E_STATE = -4,    /* e.g. render before upload_scene / set_camera                */
+  GSPLAT_E_NCCL = -5      /* NCCL unavailable or failed (message has ncclGetErrorString)  */
 } gsplat_status;
 
 typedef struct gsplat_ctx gsplat_ctx;
@@ -199,6 +200,47 @@ int gsplat_bin_projected(gsplat_ctx *ctx, const float *depth, const int32_t *rec
  * known-answer tests. */
 int gsplat_sort_pairs(gsplat_ctx *ctx, uint32_t *keys, uint32_t *values, size_t n, int begin_bit,
                       int end_bit);
+
+/* ---- several GPUs of one process ---------------------------------------------
+ * The reference drives ONE device (numIpus = 1, numReplicas = 1: src/main/splat.cpp:41-46); its unit
+ * of parallelism is the framebuffer tile (one GSplat vertex per tile, ipu_rasteriser.cpp:334-385).
+ * A group is the same IpuSplatter-shaped object over several B200s of this process:
+ *   GSPLAT_GROUP_VIEWS  whole frames go to the member devices in turn (multi-view batches, orbits);
+ *                       no inter-GPU traffic, each member streams its own frames to the host.
+ *   GSPLAT_GROUP_BANDS  every frame is cut into tile-row bands, one per member (the scene is
+ *                       replicated: it does not shard, transmittance is order dependent).  Each member
+ *                       projects the whole scene and bins / sorts / blends its band; the BGR8 rows and
+ *                       the band's tile counts are gathered on devices[0] with grouped ncclSend /
+ *                       ncclRecv and delivered from there.  Cuts are re-balanced for every frame on the
+ *                       per-tile counts (getIPUHistogram, ipu_rasteriser.cpp:104-106) of the newest
+ *                       frame already acquired: no frame waits for the host.
+ * cfg is the member configuration (cfg->device and the band fields are ignored).  The frame stream is
+ * the context's: gsplat_group_render_streamed returns at once with a ticket, gsplat_group_acquire_frame
+ * waits for that frame and hands out pointers into pinned host memory (valid until
+ * gsplat_group_max_outstanding() further frames have been rendered).  NCCL is bound at run time
+ * (libnccl.so.2); without it GSPLAT_GROUP_BANDS over more than one device fails with GSPLAT_E_NCCL. */
+typedef struct gsplat_group gsplat_group;
+#define GSPLAT_GROUP_VIEWS 0
+#define GSPLAT_GROUP_BANDS 1
+int gsplat_create_group(const gsplat_config *cfg, const int *devices, int n, int mode, gsplat_group **out);
+void gsplat_destroy_group(gsplat_group *grp);
+const char *gsplat_group_last_error(const gsplat_group *grp); /* grp may be NULL: last create error */
+int gsplat_group_size(const gsplat_group *grp);
+int gsplat_group_upload_scene(gsplat_group *grp, const float *gaussians16, size_t n);
+int gsplat_group_set_camera(gsplat_group *grp, const float modelview[16], const float projection[16], float fov,
+                            float scale_div);
+int gsplat_group_render_streamed(gsplat_group *grp, uint64_t *ticket);
+int gsplat_group_acquire_frame(gsplat_group *grp, uint64_t ticket, const uint8_t **bgr8, const uint32_t **counts);
+int gsplat_group_max_outstanding(const gsplat_group *grp); /* tickets that may be rendered ahead of the acquired one */
+int gsplat_group_sync(gsplat_group *grp);
+/* GSPLAT_GROUP_BANDS: the n + 1 tile-row cuts the NEXT frame will use. Returns the count written. */
+int gsplat_group_get_bands(const gsplat_group *grp, int *cuts, int capacity);
+/* The member context of devices[index] (stats, parity taps; owned by the group). */
+gsplat_ctx *gsplat_group_member(gsplat_group *grp, int index);
+/* The band balancer by itself (host only): tile rows -> n_bands contiguous bands of nearly equal
+ * predicted blend cost, cost of a tile = (count + 64) * tile_pixels; cuts[n_bands + 1]. */
+int gsplat_balance_bands(const uint32_t *tile_counts, int tiles_across, int tiles_down, int tile_pixels, int n_bands,
+                         int *cuts);
 
 /* ---- helpers ------------------------------------------------------------------------------- */
 /* Pinned host memory for frame read-back buffers (cudaHostAlloc / cudaFreeHost). */

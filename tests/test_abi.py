@@ -133,17 +133,36 @@ def test_product_does_not_import_the_oracle():
                 assert "pyoracle" not in txt and "liboracle" not in txt and "splat_ref" not in txt, os.path.join(dp, f)
 
 
-def _build_shim_smoke(tmpdir):
+def _build_cpp(tmpdir, name):
     import subprocess
-    exe = os.path.join(tmpdir, "shim_smoke")
+    exe = os.path.join(tmpdir, name)
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
-    libdir = os.path.dirname(sp.LIB_PATH)
+    libdir = os.path.join(ROOT, "gaussian_splat_ipu_b200")
     cmd = [cxx, "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"),
-           os.path.join(ROOT, "tests", "cpp", "shim_smoke.cpp"), "-o", exe, "-L", libdir, "-lgsplat_b200",
+           os.path.join(ROOT, "tests", "cpp", name + ".cpp"), "-o", exe, "-L", libdir, "-lgsplat_b200",
            f"-Wl,-rpath,{libdir}"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     return exe
+
+
+def _build_shim_smoke(tmpdir):
+    return _build_cpp(tmpdir, "shim_smoke")
+
+
+def test_group_host_compiles_and_group_arguments_are_checked(tmp_path):
+    """tests/cpp/group_smoke.cpp (a C++ host over gsplat_create_group) compiles warning-free and
+    links; bad group arguments are refused without touching a device."""
+    _build_cpp(str(tmp_path), "group_smoke")
+    lib = sp.load_library()
+    cfg = sp.Config()
+    lib.gsplat_config_default(C.byref(cfg))
+    h = C.c_void_p()
+    one = (C.c_int * 2)(0, 0)
+    assert lib.gsplat_create_group(C.byref(cfg), one, 2, 1, C.byref(h)) == -1 and b"twice" in lib.gsplat_group_last_error(None)
+    assert lib.gsplat_create_group(C.byref(cfg), one, 0, 1, C.byref(h)) == -1
+    assert lib.gsplat_create_group(C.byref(cfg), one, 1, 7, C.byref(h)) == -1
+    assert lib.gsplat_group_render_streamed(None, None) == -1 and lib.gsplat_group_size(None) == 0
 
 
 def test_host_only_synth_library_is_the_same_generator():

@@ -124,3 +124,23 @@ def test_gather_bands_gloo_world2():
         assert p.exitcode == 0
     assert all(ok for _, ok, _ in res), res
     assert res[0][2] == res[1][2], "ranks disagree on the band cuts"
+
+
+def test_native_band_balancer_equals_the_python_mirror():
+    """gsplat_balance_bands (what gsplat_create_group's GSPLAT_GROUP_BANDS mode cuts every frame with,
+    host only) gives exactly sharding.balance_bands(sharding.row_costs(...)) — the rule the gloo
+    world-2 test above exercises."""
+    from gaussian_splat_ipu_b200.splatter import balance_bands_native
+    rng = np.random.default_rng(8)
+    for TA, TD in ((40, 36), (60, 54), (120, 108), (4, 3)):
+        for n in (1, 2, 3, 4, 8):
+            for k in range(6):
+                counts = rng.integers(0, 4000, TA * TD).astype(np.uint32)
+                if k == 0:
+                    counts[:] = 0
+                if k == 1:
+                    counts[: TA * (TD // 2)] = 0          # everything in the lower half
+                if k == 2:
+                    counts[TA * (TD // 3): TA * (TD // 3 + 1)] *= 200   # one very heavy row
+                want = sh.balance_bands(sh.row_costs(counts, TA, 640), n)
+                assert balance_bands_native(counts, TA, TD, n, 640) == want, (TA, TD, n, k)
