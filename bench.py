@@ -647,70 +647,68 @@ def ply_orbit_arm(args):
 
 
 def bands_arm(args):
-    """Secondary mode (BASELINE configs[3]): ONE frame per step split into tile-row
-    bands over the N GPUs ("strong" scaling).  Every rank projects the whole replicated scene but
-    bins/sorts/blends only its band; band cuts are re-balanced every frame from the previous
-    frame's per-tile counts; BGR8 bands are gathered to rank 0 over NCCL point-to-point ops."""
-    import torch
-    from gaussian_splat_ipu_b200.splatter import B200Splatter
-    from gaussian_splat_ipu_b200 import sharding as sh
-    rank, world, local = dist_env()
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    """Secondary mode (BASELINE configs[3]): ONE frame per step cut into tile-row bands
+    over the N GPUs ("strong" scaling), through the library's group API (gsplat_create_group,
+    GSPLAT_GROUP_BANDS) from ONE process: every member projects the whole replicated scene but bins /
+    sorts / blends only its band; cuts are re-balanced for every frame on the per-tile counts of the
+    newest delivered frame (no host wait); BGR8 bands and counts are gathered on GPU 0 with grouped
+    ncclSend / ncclRecv and delivered to pinned host memory.  Launch as plain `python bench.py --mode
+    bands --gpus N` (under torchrun only rank 0 works).  The figure is end to end by construction."""
+    from gaussian_splat_ipu_b200.splatter import B200Group, GROUP_BANDS, launch_count
+    rank, _, _ = dist_env()
+    if rank != 0:
+        return
     scn = make_scene(args.workload)
     g, proj, W, H, views = scn.g, scn.proj, scn.W, scn.H, scn.views
-    s = B200Splatter(g, W, H, device=local, concurrent_frames=1)   # its device image is read in place
-    s.updateProjection(proj)
-    s.updateFocalLengths(FOV, scn.scale_div)
-    bgr_ptr, _ = s.device_pointers()
-    image = torch.as_tensor(sh.DeviceArray(bgr_ptr, (H * W * 3,), "|u1"), device=f"cuda:{local}")
-    counts_dev = torch.zeros(s.num_tiles, dtype=torch.int32, device=f"cuda:{local}")
-    cuts = [round(s.tiles_down * i / world) for i in range(world + 1)]
-    imb = []
+    N = args.gpus
+    grp = B200Group(g, list(range(N)), GROUP_BANDS, W, H)
+    grp.updateProjection(proj)
+    grp.updateFocalLengths(FOV, scn.scale_div)
+    depth = max(1, grp.max_outstanding - 1)
+    checksum = [0]
 
-    def step(k):
-        nonlocal cuts
-        s.updateModelView(views[k % len(views)])
-        s.set_band(cuts[rank], cuts[rank + 1])
-        s.execute()
-        s.postprocess_bgr8()
-        counts = s.getIPUHistogram()                     # waits for the frame; this rank's band only
-        if dist is not None:
-            counts_dev.copy_(torch.from_numpy(counts.astype(np.int32)))
-            sh.gather_bands(image, cuts, s.tile_h, W, 3, dst=0)
-            sh.allgather_tile_counts(counts_dev)
-            counts = counts_dev.cpu().numpy()
-        cost = sh.row_costs(counts, s.tiles_across, s.tile_w * s.tile_h)
-        imb.append(sh.band_imbalance(cost, cuts))
-        cuts = sh.balance_bands(cost, world)             # for the NEXT frame
+    def run(first, count):
+        inflight = []
+        for k in range(first, first + count):
+            grp.updateModelView(views[k % len(views)])
+            inflight.append(grp.executeStreamed())
+            if len(inflight) > depth:
+                img, counts = grp.acquireFrame(inflight.pop(0))
+                checksum[0] += int(img[H // 2, ::64, 1].sum()) + int(counts[0])
+        for t in inflight:
+            img, counts = grp.acquireFrame(t)
+        return img, counts
 
-    for k in range(args.warmup):
-        step(k)
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
+    run(0, PREWARM_FRAMES + args.warmup)
+    grp.sync()
+    samplers = [ClockSampler(d) for d in range(N)]
+    for sm in samplers:
+        sm.arm()
+    l0 = launch_count()
     t0 = time.perf_counter()
-    for k in range(args.steps):
-        step(args.warmup + k)
-    torch.cuda.synchronize()
-    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-    fps = args.steps / float(dt.item())
-    if rank == 0:
-        chk = int(image[::97].to(torch.int64).sum().item())
-        print(json.dumps({"metric": "frames_per_second", "mode": "tile-row bands of one frame", "value": fps,
-                          "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                          "ms_per_step": 1e3 / fps, "higher_is_better": True, "scaling": "strong", "dtype": "f32",
-                          "data": "synthetic", "config": {"workload": args.workload, "width": W, "height": H,
-                                                          "gaussians": int(g.shape[0])},
-                          "band_imbalance_mean": float(np.mean(imb[args.warmup:])), "last_cuts": cuts,
-                          "gathered_bytes_per_step": W * H * 3, "checksum": chk}), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+    img, counts = run(args.warmup, args.steps)
+    grp.sync()
+    dt = time.perf_counter() - t0
+    launches = launch_count() - l0
+    clocks = [sm.finish() for sm in samplers]
+    fps = args.steps / dt
+    cuts = grp.bands()
+    cost = np.asarray(counts, np.float64).reshape(grp.tiles_down, grp.tiles_across).sum(axis=1) + 64.0 * grp.tiles_across
+    per = np.array([cost[a:b].sum() for a, b in zip(cuts[:-1], cuts[1:])])
+    line = {"metric": "frames_per_second", "mode": "tile-row bands of one frame (gsplat_create_group, GSPLAT_GROUP_BANDS)",
+            "value": fps, "unit": "frames/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": scn.data, "config": scn.config(),
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 136 * N,
+                    "d2h_bytes_per_step": W * H * 3 + grp.num_tiles * 4,
+                    "api": "gsplat_group_render_streamed / gsplat_group_acquire_frame, every frame delivered to pinned host memory"},
+            "tickets_outstanding": depth, "gpu_launches": int(launches), "last_cuts": cuts,
+            "band_cost_imbalance": float(per.max() / max(per.mean(), 1e-30)),
+            "gathered_bytes_per_step": int((W * H * 3 + grp.num_tiles * 4) * (1 - (cuts[1] - cuts[0]) / max(grp.tiles_down, 1))),
+            "clocks": clocks[0], "clocks_all": clocks,
+            "checksum": int(img[::7, ::7].astype(np.uint64).sum()) + int(counts.sum()) + (checksum[0] & 0)}
+    print(json.dumps(line), flush=True)
+    grp.close()
 
 
 def multiview_arm(args):

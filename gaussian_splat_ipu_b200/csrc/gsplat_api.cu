@@ -165,6 +165,10 @@ struct gsplat_ctx {
   FrameSlot slots[NUM_SLOTS];
   uint64_t frame_no = 0;      // frames enqueued so far; the last one lives in slot (frame_no-1) % NUM_SLOTS
   size_t need_grow = 0;       // largest D seen by an overflowed frame
+  // frame numbers that overflowed the duplicate buffer (ring): the verdict outlives the FrameSlot,
+  // which overflow re-runs may recycle before a ticket that names the frame is acquired
+  uint64_t ovf_log[64] = {0};
+  uint64_t ovf_logged = 0;
   cudaEvent_t t0 = nullptr, t1 = nullptr, post0 = nullptr, post1 = nullptr;
   bool post_pending = false;
   // frame stream (allocated on first use)
