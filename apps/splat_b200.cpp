@@ -5,11 +5,16 @@
 // frame as a PPM and print the frame rate.  No Boost / OpenCV / spdlog / Poplar: plain C++17.
 //
 //   splat_b200 --input scene.ply [--width 1280] [--height 720] [--frames 32] [--scale-div 0.1]
-//              [--out frame.ppm] [--device 0] [--cache scene.gsc]
+//              [--out frame.ppm] [--device 0] [--cache scene.gsc] [--cache-only]
 //   splat_b200 --synthetic 1000000 ...          (SURVEY §8d generator instead of a PLY)
 //
 // What replaces what (reference file:line):
-//   PLY reading                 happly via src/splat/file_io.cpp:30-42,62-77 -> read_ply() below
+//   PLY reading                 happly via src/splat/file_io.cpp:30-42,62-77: the SAME happly calls when built
+//                               with -DGSPLAT_WITH_HAPPLY (apps/Makefile does when include/happly.h of the
+//                               reference tree is reachable: in the reference's own tree it always is), else
+//                               the built-in reader below; both give bit-identical records (tests/test_host_inputs.py)
+//   tracing                     pvti tracepoints "splatter" / mvp_transform_ipu / ui_update (splat.cpp:69,210,258)
+//                               -> NVTX ranges of the same names
 //   PLY -> Gaussian3D           src/main/splat.cpp:136-163 (SH_C0 colour, raw opacity / rot / log-scale)
 //   recentre + z-negate         src/main/splat.cpp:93-100
 //   projection                  src/main/splat.cpp:186-195, src/splat/camera.cpp:10-15, src/splat/geometry.cpp:9-24
@@ -28,6 +33,18 @@
 #include <vector>
 
 #include "gsplat_b200.hpp"
+#ifdef GSPLAT_WITH_HAPPLY
+#include <happly.h>   // the reference's vendored loader (include/happly.h), not part of this repository
+#endif
+#if __has_include(<nvtx3/nvToolsExt.h>)
+#include <nvtx3/nvToolsExt.h>   // header-only (dlopens the injection library when a tool is attached)
+struct TraceScope {   // pvti::Tracepoint's role (src/main/splat.cpp:210-258)
+  explicit TraceScope(const char *name) { nvtxRangePushA(name); }
+  ~TraceScope() { nvtxRangePop(); }
+};
+#else
+struct TraceScope { explicit TraceScope(const char *) {} };
+#endif
 
 namespace {
 
@@ -119,8 +136,8 @@ Mat4 app_projection(Vec3 bmin, Vec3 bmax, float fov, float aspect) {
 
 // Binary-little-endian PLY with float vertex properties (what happly reads for the reference,
 // src/splat/file_io.cpp:30-42,62-77).  Returns one column per requested property.
-bool read_ply(const std::string &path, const std::vector<std::string> &want, std::vector<std::vector<float>> &cols,
-              std::size_t &n, std::string &err) {
+[[maybe_unused]] bool read_ply(const std::string &path, const std::vector<std::string> &want,
+                               std::vector<std::vector<float>> &cols, std::size_t &n, std::string &err) {
   std::ifstream fh(path, std::ios::binary);
   if (!fh) { err = "cannot open " + path; return false; }
   std::vector<std::string> names;
@@ -158,13 +175,35 @@ bool read_ply(const std::string &path, const std::vector<std::string> &want, std
   return true;
 }
 
+#ifdef GSPLAT_WITH_HAPPLY
+// The reference's loader: happly::PLYData + getElement("vertex").getProperty<float>(name) for the 14
+// properties, exactly the calls of fillProperty / fillPlyProperties (src/splat/file_io.cpp:57-77).
+bool read_ply_happly(const std::string &path, const std::vector<std::string> &want, std::vector<std::vector<float>> &cols,
+                     std::size_t &n, std::string &err) {
+  try {
+    happly::PLYData plyData(path);
+    cols.clear();
+    for (const auto &name : want) cols.push_back(plyData.getElement("vertex").getProperty<float>(name));
+    n = cols.empty() ? 0 : cols[0].size();
+  } catch (const std::exception &e) {
+    err = e.what();
+    return false;
+  }
+  return true;
+}
+#endif
+
 // src/main/splat.cpp:136-163 + :93-100
 bool gaussians_from_ply(const std::string &path, std::vector<splat::Gaussian3DRecord> &g, std::string &err) {
   const std::vector<std::string> want = {"x", "y", "z", "f_dc_0", "f_dc_1", "f_dc_2", "opacity", "scale_0", "scale_1",
                                          "scale_2", "rot_0", "rot_1", "rot_2", "rot_3"};
   std::vector<std::vector<float>> c;
   std::size_t n = 0;
+#ifdef GSPLAT_WITH_HAPPLY
+  if (!read_ply_happly(path, want, c, n, err)) return false;
+#else
   if (!read_ply(path, want, c, n, err)) return false;
+#endif
   g.resize(n);
   const float SH_C0 = 0.28209479177387814f;
   for (std::size_t i = 0; i < n; ++i) {
@@ -246,6 +285,8 @@ int main(int argc, char **argv) {
   const std::string out = arg(argc, argv, "--out", "");
   const int device = std::atoi(arg(argc, argv, "--device", "0"));
   const std::string cache = arg(argc, argv, "--cache", "");   // scene cache: read if present, else written after the PLY conversion
+  bool cache_only = false;                                     // stop after the scene is built / cached (no device needed)
+  for (int i = 1; i < argc; ++i) cache_only = cache_only || !std::strcmp(argv[i], "--cache-only");
   if (input.empty() && !synthetic && cache.empty()) {
     std::fprintf(stderr, "usage: %s --input scene.ply | --synthetic N  [--width W --height H --frames K --scale-div D "
                          "--out frame.ppm --device I --cache scene.gsc]\n", argv[0]);
@@ -270,6 +311,10 @@ int main(int argc, char **argv) {
     recentre_negate_z(g, bmin, bmax);
     if (!cache.empty() && !cache_write(cache, g, bmin, bmax)) std::fprintf(stderr, "cannot write scene cache %s\n", cache.c_str());
   }
+  if (cache_only) {
+    std::printf("ok gaussians %zu cache %s\n", g.size(), cache.c_str());
+    return 0;
+  }
   const float fov = 40.0f * 0.017453292519943295f;   // glm::radians(40.f), splat.cpp:170
   const Mat4 proj = app_projection(bmin, bmax, fov, (float)W / (float)H);
   const Mat4 base = mvp_start();
@@ -283,6 +328,7 @@ int main(int argc, char **argv) {
     const std::size_t depth = 2 * (std::size_t)s.concurrentFrames();   // tickets outstanding: two per frame in flight
     unsigned long long pixel_sum = 0, count_sum = 0;
     auto deliver = [&](std::uint64_t ticket) {   // what the AsyncTask thread does with imagePtrBuffered
+      TraceScope trace("ui_update");
       s.acquireFrame(ticket, &bgr, &counts);
       pixel_sum = 0; count_sum = 0;
       for (std::size_t i = 0; i < (std::size_t)W * H * 3; i += 97) pixel_sum += bgr[i];
@@ -291,6 +337,7 @@ int main(int argc, char **argv) {
     const auto t0 = std::chrono::steady_clock::now();
     for (int k = 0; k < frames; ++k) {
       // config 2 orbit: glm::rotate(mvpStart, radians(360 / frames * k), (0,1,0))
+      TraceScope trace("mvp_transform_ipu");
       s.updateModelView(rotate(base, (360.0f / (float)frames * (float)k) * 0.017453292519943295f, {0.f, 1.f, 0.f}));
       inflight.push_back(s.executeStreamed());
       if (inflight.size() > depth) { deliver(inflight.front()); inflight.erase(inflight.begin()); }

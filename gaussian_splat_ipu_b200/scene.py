@@ -93,9 +93,33 @@ def gaussians_from_ply(ply: dict[str, np.ndarray]) -> np.ndarray:
 
 
 # ----------------------------------------------------------------------------- glm restatements
+# glm::tan / cos / sin on floats are the C library's tanf / cosf / sinf: call those (numpy's SIMD
+# kernels round the last bit differently for some arguments), so the matrices below are bit-identical
+# to the ones the reference's host code builds (tests/test_host_inputs.py).
+def _libm_f32(name, fallback):
+    try:
+        import ctypes
+        fn = getattr(ctypes.CDLL("libm.so.6"), name)
+        fn.restype, fn.argtypes = ctypes.c_float, [ctypes.c_float]
+        return lambda x: F32(fn(float(F32(x))))
+    except (OSError, AttributeError):
+        return lambda x: fallback(F32(x), dtype=F32)
+
+
+_tanf, _cosf, _sinf = _libm_f32("tanf", np.tan), _libm_f32("cosf", np.cos), _libm_f32("sinf", np.sin)
+
+
+def _dot3(a, b):
+    """glm::dot for vec3 (detail/func_geometric.inl): tmp = a * b; tmp.x + tmp.y + tmp.z, every step
+    rounded to f32 (np.dot goes through BLAS, which may fuse or reorder)."""
+    a, b = np.asarray(a, dtype=F32), np.asarray(b, dtype=F32)
+    t = a * b
+    return F32(F32(t[0] + t[1]) + t[2])
+
+
 def _normalize(v):
     v = np.asarray(v, dtype=F32)
-    return v * (F32(1.0) / np.sqrt(np.dot(v, v), dtype=F32))
+    return v * (F32(1.0) / np.sqrt(_dot3(v, v), dtype=F32))
 
 
 def look_at(eye, center, up) -> np.ndarray:
@@ -108,9 +132,9 @@ def look_at(eye, center, up) -> np.ndarray:
     m[0, 0], m[1, 0], m[2, 0] = s
     m[0, 1], m[1, 1], m[2, 1] = u
     m[0, 2], m[1, 2], m[2, 2] = -f
-    m[3, 0] = -np.dot(s, eye)
-    m[3, 1] = -np.dot(u, eye)
-    m[3, 2] = np.dot(f, eye)
+    m[3, 0] = -_dot3(s, eye)
+    m[3, 1] = -_dot3(u, eye)
+    m[3, 2] = _dot3(f, eye)
     return m
 
 
@@ -131,7 +155,7 @@ def frustum(left, right, bottom, top, near, far) -> np.ndarray:
 def rotate(m: np.ndarray, angle: float, axis) -> np.ndarray:
     """glm::rotate(m, angle, axis) (ext/matrix_transform.inl:18-46)."""
     a = F32(angle)
-    c, s = np.cos(a, dtype=F32), np.sin(a, dtype=F32)
+    c, s = _cosf(a), _sinf(a)
     ax = _normalize(axis)
     t = (F32(1) - c) * ax
     r = np.zeros((3, 3), dtype=F32)
@@ -174,7 +198,7 @@ def look_at_bounding_box(bb, up=(0.0, 1.0, 1.0), scale=1.0) -> np.ndarray:
     """``src/splat/camera.cpp:10-15``."""
     bmin, bmax = bb
     centre = (bmax + bmin) * F32(0.5)
-    radius = np.sqrt(np.dot(bmax - bmin, bmax - bmin), dtype=F32) * F32(0.5)
+    radius = np.sqrt(_dot3(bmax - bmin, bmax - bmin), dtype=F32) * F32(0.5)
     eye = centre - np.array([0, 0, F32(scale) * radius], dtype=F32)
     return look_at(eye, centre, up)
 
@@ -183,8 +207,8 @@ def fit_frustum_to_bounding_box(bb, fov_radians: float, aspect: float) -> np.nda
     """``src/splat/geometry.cpp:9-24`` (near = R/tan(fov), far = near + 20R)."""
     bmin, bmax = bb
     d = (bmax - bmin).astype(F32)
-    radius = np.sqrt(np.dot(d, d), dtype=F32) * F32(0.5)
-    near = radius / np.tan(F32(fov_radians), dtype=F32)
+    radius = np.sqrt(_dot3(d, d), dtype=F32) * F32(0.5)
+    near = radius / _tanf(fov_radians)
     far = near + F32(20) * radius
     hw, hh = radius * F32(aspect), radius
     return frustum(-hw, hw, -hh, hh, near, far)
@@ -237,7 +261,7 @@ def multiview_cameras(g16: np.ndarray, n_orbit: int = 32, n_spiral: int = 32) ->
     bb = bounds(g16[:, 0:3])
     bmin, bmax = bb
     centre = (bmax + bmin) * F32(0.5)
-    radius = np.sqrt(np.dot(bmax - bmin, bmax - bmin), dtype=F32) * F32(0.5)
+    radius = np.sqrt(_dot3(bmax - bmin, bmax - bmin), dtype=F32) * F32(0.5)
     base = look_at_bounding_box(bb, (0.0, 1.0, 1.0), 1.0)
     views = [rotate(base, np.radians(F32(360.0 / n_orbit * k)), (0.0, 1.0, 0.0)) for k in range(n_orbit)]
     for k in range(n_spiral):

@@ -17,11 +17,15 @@ from __future__ import annotations
 import numpy as np
 
 
-def row_costs(tile_counts: np.ndarray, tiles_across: int, tile_pixels: int = 640, fixed: float = 64.0) -> np.ndarray:
+def row_costs(tile_counts: np.ndarray, tiles_across: int, tile_pixels: int = 640, fixed: float = 64.0,
+              cap: float = 2048.0) -> np.ndarray:
     """Predicted cost of every tile row from per-tile list lengths (a11): blend work is
-    pixels x list length per tile; `fixed` stands for the per-tile constant (launch, framebuffer
-    write) so that empty rows are not free."""
-    c = np.asarray(tile_counts, dtype=np.float64).reshape(-1, tiles_across)
+    pixels x list entries walked per tile; `fixed` stands for the per-tile constant (launch,
+    framebuffer write) so that empty rows are not free.  `cap`: pixels stop at T(1-alpha) < 1e-4
+    (codelets.cpp:405-408), so the entries a tile walks saturate (measured: 1000-1900 per pixel on
+    the most expensive tiles, whatever the list length).  Mirror of the library's balancer
+    (gsplat_balance_bands, csrc/gsplat_group.inc)."""
+    c = np.minimum(np.asarray(tile_counts, dtype=np.float64), cap).reshape(-1, tiles_across)
     return (c * tile_pixels + fixed * tile_pixels).sum(axis=1)
 
 

@@ -52,6 +52,12 @@ PRO
 } | ${HOSTCXX:-/usr/bin/g++} -x c++ -std=c++20 -O2 -ffp-contract=off -fopenmp -fPIC -shared -w \
         -I "$HERE/poplar_stub" -I "$REF/external/glm" -I "$REF/include/math" \
         -o "$OUT/libsplat_ref.so" -
+# Second library: the reference's host-side INPUT code (PLY loading through happly, camera, frustum),
+# compiled UNCHANGED from its own translation units, plus oracle/ref_host_driver.cpp (ours).
+${HOSTCXX:-/usr/bin/g++} -std=c++20 -O2 -ffp-contract=off -fPIC -shared -w \
+    -I "$REF/include" -I "$REF/external/glm" \
+    "$REF/src/splat/file_io.cpp" "$REF/src/splat/camera.cpp" "$REF/src/splat/geometry.cpp" \
+    "$HERE/ref_host_driver.cpp" -o "$OUT/libhost_ref.so"
 # scene inputs (data, not source) so PLY-scene parity tests can run where /root/reference is absent
 mkdir -p "$OUT/data"
 for p in "$REF"/data/point_cloud_*.ply; do

@@ -225,3 +225,91 @@ def detile(fb_tiled: np.ndarray, W: int, H: int, tile_w=32, tile_h=20) -> np.nda
 def psnr(a: np.ndarray, b: np.ndarray, peak: float = 1.0) -> float:
     mse = float(np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2))
     return float("inf") if mse == 0 else 10.0 * np.log10(peak * peak / mse)
+
+
+# ---- the reference's host-side INPUT code (oracle/_ref/libhost_ref.so) --------------------------------
+HOST_SO = os.path.join(HERE, "_ref", "libhost_ref.so")
+
+
+def have_host_ref() -> bool:
+    return os.path.exists(HOST_SO)
+
+
+class HostRef:
+    """The reference's own PLY loading (happly via src/splat/file_io.cpp), lookAtBoundingBox
+    (src/splat/camera.cpp), fitFrustumToBoundingBox (src/splat/geometry.cpp) and glm, compiled
+    unchanged (oracle/build_ref.sh) behind oracle/ref_host_driver.cpp.  Pins scene.py and the C++
+    host driver to the reference.  TEST INFRASTRUCTURE."""
+
+    def __init__(self):
+        if not os.path.exists(HOST_SO):
+            raise FileNotFoundError(HOST_SO)
+        lib = self.lib = C.CDLL(HOST_SO)
+        lib.refhost_open.restype = C.c_void_p
+        lib.refhost_open.argtypes = [C.c_char_p]
+        lib.refhost_error.restype = C.c_char_p
+        lib.refhost_error.argtypes = [C.c_void_p]
+        lib.refhost_close.argtypes = [C.c_void_p]
+        lib.refhost_count.restype = C.c_size_t
+        lib.refhost_count.argtypes = [C.c_void_p]
+        lib.refhost_properties.argtypes = [C.c_void_p, _fp]
+        lib.refhost_gaussians.argtypes = [C.c_void_p, _fp]
+        lib.refhost_bounds.argtypes = [C.c_void_p, _fp, _fp]
+        lib.refhost_look_at_bounding_box.argtypes = [_fp, _fp, _fp, C.c_float, _fp]
+        lib.refhost_fit_frustum.argtypes = [_fp, _fp, C.c_float, C.c_float, _fp]
+        lib.refhost_app_projection.argtypes = [_fp, _fp, C.c_float, C.c_float, _fp]
+        lib.refhost_orbit_view.argtypes = [C.c_float, _fp]
+        lib.refhost_ui_view.argtypes = [_fp] + [C.c_float] * 5 + [_fp]
+        lib.refhost_rotate.argtypes = [_fp, C.c_float, _fp, _fp]
+
+    @staticmethod
+    def _p(a):
+        return np.ascontiguousarray(a, np.float32).ctypes.data_as(_fp)
+
+    def load(self, path: str):
+        """(properties n x 14 in file_io.cpp:62-77 order, Gaussian3D records n x 16, bbox min, bbox max)
+        after the app's recentre + z-negate."""
+        h = self.lib.refhost_open(path.encode())
+        try:
+            err = self.lib.refhost_error(h)
+            if err:
+                raise RuntimeError(err.decode())
+            n = int(self.lib.refhost_count(h))
+            props = np.empty((n, 14), np.float32)
+            g16 = np.empty((n, 16), np.float32)
+            bmin, bmax = np.empty(3, np.float32), np.empty(3, np.float32)
+            self.lib.refhost_properties(h, props.ctypes.data_as(_fp))
+            self.lib.refhost_gaussians(h, g16.ctypes.data_as(_fp))
+            self.lib.refhost_bounds(h, bmin.ctypes.data_as(_fp), bmax.ctypes.data_as(_fp))
+        finally:
+            self.lib.refhost_close(h)
+        return props, g16, bmin, bmax
+
+    def _mat(self, fn, *args):
+        out = np.empty(16, np.float32)
+        fn(*args, out.ctypes.data_as(_fp))
+        return out.reshape(4, 4)
+
+    def look_at_bounding_box(self, bmin, bmax, up, scale):
+        a, b, u = (np.ascontiguousarray(x, np.float32) for x in (bmin, bmax, up))
+        return self._mat(self.lib.refhost_look_at_bounding_box, a.ctypes.data_as(_fp), b.ctypes.data_as(_fp),
+                         u.ctypes.data_as(_fp), float(scale))
+
+    def fit_frustum(self, bmin, bmax, fov, aspect):
+        a, b = (np.ascontiguousarray(x, np.float32) for x in (bmin, bmax))
+        return self._mat(self.lib.refhost_fit_frustum, a.ctypes.data_as(_fp), b.ctypes.data_as(_fp), float(fov), float(aspect))
+
+    def app_projection(self, bmin, bmax, fov, aspect):
+        a, b = (np.ascontiguousarray(x, np.float32) for x in (bmin, bmax))
+        return self._mat(self.lib.refhost_app_projection, a.ctypes.data_as(_fp), b.ctypes.data_as(_fp), float(fov), float(aspect))
+
+    def orbit_view(self, degrees):
+        return self._mat(self.lib.refhost_orbit_view, float(degrees))
+
+    def ui_view(self, model_view, env_deg, env_deg2, X, Y, Z):
+        m = np.ascontiguousarray(model_view, np.float32)
+        return self._mat(self.lib.refhost_ui_view, m.ctypes.data_as(_fp), float(env_deg), float(env_deg2), float(X), float(Y), float(Z))
+
+    def rotate(self, m, angle, axis):
+        mm, ax = np.ascontiguousarray(m, np.float32), np.ascontiguousarray(axis, np.float32)
+        return self._mat(self.lib.refhost_rotate, mm.ctypes.data_as(_fp), float(angle), ax.ctypes.data_as(_fp))

@@ -31,3 +31,5 @@ print("top tiles by cycles: (tile, row, col, count, visited pairs, visited/px, c
 for t in order[:12]:
     print("  ", int(t), int(t) // s.tiles_across, int(t) % s.tiles_across, int(cnt[t]), int(prs[t]),
           round(int(prs[t]) / (s.tile_w * s.tile_h), 1), int(cyc[t]))
+if len(sys.argv) > 3:       # raw per-tile arrays for fitting a cost model (band balancing)
+    np.savez_compressed(sys.argv[3], counts=cnt, cycles=cyc, pairs=prs, tiles_across=s.tiles_across, timings=np.array(list(s.timings().values())))
