@@ -7,6 +7,8 @@
 //   splat_b200 --input scene.ply [--width 1280] [--height 720] [--frames 32] [--scale-div 0.1]
 //              [--out frame.ppm] [--device 0] [--cache scene.gsc] [--cache-only]
 //   splat_b200 --synthetic 1000000 ...          (SURVEY §8d generator instead of a PLY)
+//   splat_b200 --input scene.ply --ui-port 5000 interactive: frames streamed to remote_render_ui over
+//                                               packetcomms, camera / fov / scale from the UI (splat.cpp:245-322)
 //
 // What replaces what (reference file:line):
 //   PLY reading                 happly via src/splat/file_io.cpp:30-42,62-77: the SAME happly calls when built
@@ -33,6 +35,9 @@
 #include <vector>
 
 #include "gsplat_b200.hpp"
+#ifdef GSPLAT_WITH_UI
+#include "stream_server.hpp"   // B200StreamServer: the reference's InterfaceServer over packetcomms
+#endif
 #ifdef GSPLAT_WITH_HAPPLY
 #include <happly.h>   // the reference's vendored loader (include/happly.h), not part of this repository
 #endif
@@ -104,6 +109,22 @@ Mat4 rotate(const Mat4 &m, float angle, Vec3 axis) {
     for (int i = 0; i < 4; ++i) out.m[k][i] = m.m[0][i] * r[k][0] + m.m[1][i] * r[k][1] + m.m[2][i] * r[k][2];
   for (int i = 0; i < 4; ++i) out.m[3][i] = m.m[3][i];
   return out;
+}
+
+// glm a * b (type_mat4x4.inl:630-648), left-to-right sums
+[[maybe_unused]] Mat4 mat_mul(const Mat4 &a, const Mat4 &b) {
+  Mat4 r{};
+  for (int c = 0; c < 4; ++c)
+    for (int k = 0; k < 4; ++k)
+      r.m[c][k] = ((a.m[0][k] * b.m[c][0] + a.m[1][k] * b.m[c][1]) + a.m[2][k] * b.m[c][2]) + a.m[3][k] * b.m[c][3];
+  return r;
+}
+
+// glm::translate (ext/matrix_transform.inl:10-15)
+[[maybe_unused]] Mat4 translate(const Mat4 &m, Vec3 v) {
+  Mat4 r = m;
+  for (int k = 0; k < 4; ++k) r.m[3][k] = m.m[0][k] * v.x + m.m[1][k] * v.y + m.m[2][k] * v.z + m.m[3][k];
+  return r;
 }
 
 Vec3 transform_point(const Mat4 &m, Vec3 p) {   // glm mat4 * vec4(p, 1), xyz
@@ -318,6 +339,72 @@ int main(int argc, char **argv) {
   const float fov = 40.0f * 0.017453292519943295f;   // glm::radians(40.f), splat.cpp:170
   const Mat4 proj = app_projection(bmin, bmax, fov, (float)W / (float)H);
   const Mat4 base = mvp_start();
+  const int ui_port = std::atoi(arg(argc, argv, "--ui-port", "0"));
+#ifdef GSPLAT_WITH_UI
+  if (ui_port) {
+    // The interactive loop of src/main/splat.cpp:245-322.  uiServer->start() blocks until the viewer has
+    // connected (InterfaceServer.hpp:272-278); per frame: the UI state gives the view
+    // (modelView * Rx(env) * Ry(env2) * T(X/50, Y/50, -Z/20 + 20), :312-314), the projection
+    // (fitFrustumToBoundingBox(bbInCamera, state.fov, aspect), :287) and fxy = (fov, lambda1 / 10) (:262);
+    // the finished frame and the tile histogram go to the viewer while the next frame renders (the
+    // AsyncTask + imagePtr / imagePtrBuffered swap, :208-225,281-283 — here the frame stream's slots).
+    try {
+      splat::B200Splatter s(g.data(), g.size(), W, H, device);
+      b200ui::B200StreamServer ui(ui_port);
+      ui.start();
+      if (!ui.connected()) { std::printf("ui: no client\n"); return 4; }
+      ui.initialiseVideoStream(W, H);
+      b200ui::B200StreamServer::State state;
+      state.fov = fov;                               // splat.cpp:175
+      ui.updateFov(state.fov);
+      const Vec3 centre = {(bmax.x + bmin.x) * .5f, (bmax.y + bmin.y) * .5f, (bmax.z + bmin.z) * .5f};
+      const Vec3 d = sub(bmax, bmin);
+      const float radius = std::sqrt(dot(d, d)) * .5f;
+      const Mat4 modelView = look_at({centre.x, centre.y, centre.z - 1.f * radius}, centre, {0.f, 1.f, 1.f});   // :186
+      Mat4 dynamicView = base, projection = proj;
+      std::vector<std::uint64_t> inflight;
+      const std::size_t depth = (std::size_t)s.concurrentFrames();
+      std::vector<std::uint32_t> hist((std::size_t)s.numTiles());
+      unsigned long long frames_sent = 0;
+      auto deliver = [&](std::uint64_t ticket) {
+        TraceScope trace("ui_update");
+        const std::uint8_t *bgr = nullptr;
+        const std::uint32_t *counts = nullptr;
+        s.acquireFrame(ticket, &bgr, &counts);
+        hist.assign(counts, counts + s.numTiles());
+        ui.sendHistogram(hist);
+        ui.sendPreviewImage(bgr, W, H, (std::size_t)W * 3);
+        ++frames_sent;
+      };
+      do {
+        {
+          TraceScope trace("mvp_transform_ipu");
+          s.updateModelView(dynamicView);
+          s.updateProjection(projection);
+          s.updateFocalLengths(state.fov, state.lambda1 / 10.f);
+          inflight.push_back(s.executeStreamed());
+        }
+        if (inflight.size() > depth) { deliver(inflight.front()); inflight.erase(inflight.begin()); }
+        state = ui.consumeState();
+        projection = app_projection(bmin, bmax, state.fov, (float)W / (float)H);
+        const float rad = 0.017453292519943295f;
+        dynamicView = mat_mul(modelView, rotate(identity(), state.envRotationDegrees * rad, {1.f, 0.f, 0.f}));
+        dynamicView = rotate(dynamicView, state.envRotationDegrees2 * rad, {0.f, 1.f, 0.f});
+        dynamicView = translate(dynamicView, {state.X / 50.f, state.Y / 50.f, -state.Z / 20.f + 20.f});
+        // a viewer that reads slower than the GPU renders must not grow the muxer's queue without bound
+        std::this_thread::sleep_for(std::chrono::microseconds(500));
+      } while (!state.stop && ui.connected());
+      while (!inflight.empty() && ui.connected()) { deliver(inflight.front()); inflight.erase(inflight.begin()); }
+      std::printf("ok ui frames %llu\n", frames_sent);
+    } catch (const std::runtime_error &e) {
+      std::printf("no-device: %s\n", e.what());
+      return 3;
+    }
+    return 0;
+  }
+#else
+  if (ui_port) { std::fprintf(stderr, "--ui-port: built without packetcomms (reference tree not reachable at build time)\n"); return 2; }
+#endif
   try {
     splat::B200Splatter s(g.data(), g.size(), W, H, device);
     s.updateProjection(proj);
