@@ -67,6 +67,11 @@ constexpr int BLEND_MAX_WARPS = 20;                  // consumer warps of an und
 #ifndef GSPLAT_BLEND_LANELIST
 #define GSPLAT_BLEND_LANELIST 1
 #endif
+// staged entries a consumer warp takes per turn of its loop (32 or 64; 64 needs the per-pixel sets).
+// Measured (profiles/ab_k5_r2.txt): 64 is SLOWER (K5 0.373-0.379 ms against 0.348-0.350): keep 32.
+#ifndef GSPLAT_BLEND_SPAN
+#define GSPLAT_BLEND_SPAN 32
+#endif
 constexpr uint32_t BLEND_FULL_ARRIVALS = GSPLAT_BLEND_TMA ? 1u : 32u;   // arrivals that complete a "full" phase
 
 struct BlendSmem {
@@ -133,7 +138,7 @@ __device__ __forceinline__ uint32_t ld_volatile_shared(const uint32_t *p) {
 // codelets.cpp:389-410; returns true when the pixel stops at this entry.
 template <bool COUNT>
 __device__ __forceinline__ bool blend_exact(const float4 b, const float4 c, float dx, float dy,
-                                            const unsigned long long *exp_tab, float &T, float &Cr, float &Cg,
+                                            const TabRef exp_tab, float &T, float &Cr, float &Cg,
                                             float &Cb, float &Ca, unsigned long long &n_blend) {
   const float power = -0.5f * (b.x * dx * dx + b.z * dy * dy) - b.y * dx * dy;
   if (power > 0.0f) return false;
@@ -269,6 +274,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
     const float bcx = (float)(tcol * 32u + sub * (uint32_t)part_w + cb * 8u) + 3.5f;
     const float bcy = (float)(trow * full_tile_h + rb * 4u) + 1.5f;
 
+    const TabRef exp_tab{smem_addr(sm.exp_tab)};
     float T = 1.f, Cr = 0.f, Cg = 0.f, Cb = 0.f, Ca = 0.f;
     bool done = !valid;
     if (!FIRST && valid) {
@@ -289,6 +295,54 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       if (!warp_done) {
         const uint32_t base = it * BLEND_BATCH, cnt = min((uint32_t)BLEND_BATCH, n - base);
         const float4 *ring = sm.ring[stage];
+#if GSPLAT_BLEND_LANELIST && GSPLAT_BLEND_SPAN == 64
+        // 64 staged entries per turn: two hit ballots, phase A over both, ONE phase B over the union —
+        // the longest per-pixel set of 64 entries is relatively shorter than of 32 (more lanes busy)
+        for (uint32_t c0 = 0; c0 < cnt; c0 += 64) {
+          uint32_t smask[2] = {0u, 0u};
+#pragma unroll
+          for (uint32_t h = 0; h < 2; ++h) {
+            const uint32_t jj = c0 + h * 32 + lane;
+            bool hit = false;
+            if (jj < cnt) {
+              const float4 a = ring[jj * 3];
+              hit = fabsf(a.x - bcx) <= a.z + 3.5f && fabsf(a.y - bcy) <= a.w + 1.5f;
+            }
+            uint32_t mask = __ballot_sync(0xffffffffu, hit);
+            const uint32_t cb0 = c0 + h * 32;
+            uint32_t sm_ = 0;
+            while (mask) {
+              const uint32_t l0 = __ffs(mask) - 1;
+              mask &= mask - 1;
+              const bool two = mask != 0;
+              const uint32_t l1 = two ? __ffs(mask) - 1 : l0;
+              mask &= mask - 1;
+              const float4 a0 = ring[(cb0 + l0) * 3], b0 = ring[(cb0 + l0) * 3 + 1];
+              const float4 a1 = ring[(cb0 + l1) * 3], b1 = ring[(cb0 + l1) * 3 + 1];
+              const float dx0 = a0.x - xf, dy0 = a0.y - yf, dx1 = a1.x - xf, dy1 = a1.y - yf;
+              const float q0 = fmaf(b0.z * dy0, dy0, dx0 * fmaf(b0.x, dx0, (b0.y + b0.y) * dy0));
+              const float q1 = fmaf(b1.z * dy1, dy1, dx1 * fmaf(b1.x, dx1, (b1.y + b1.y) * dy1));
+              sm_ |= (q0 <= b0.w ? 1u << l0 : 0u) | (two && q1 <= b1.w ? 1u << l1 : 0u);
+            }
+            smask[h] = done ? 0u : sm_;
+          }
+          unsigned long long todo = (unsigned long long)smask[0] | ((unsigned long long)smask[1] << 32);
+          while (__any_sync(0xffffffffu, todo != 0ull)) {
+            if (todo) {
+              const uint32_t k = c0 + (uint32_t)__ffsll((long long)todo) - 1u;
+              todo &= todo - 1ull;
+              const float4 *e = ring + k * 3;
+              const float2 mxy = *reinterpret_cast<const float2 *>(e);
+              if (blend_exact<COUNT>(e[1], e[2], mxy.x - xf, mxy.y - yf, exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
+                done = true;
+                todo = 0ull;
+                if (COUNT) stop_at = base + k + 1;
+              }
+            }
+          }
+          if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
+        }
+#else
         for (uint32_t c0 = 0; c0 < cnt; c0 += 32) {
           // lane = entry: does the box around its alpha >= 1/255 ellipse reach this warp's block?
           const uint32_t jj = c0 + lane;
@@ -325,7 +379,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
               smask &= smask - 1;
               const float4 *e = ring + (c0 + kl) * 3;
               const float2 mxy = *reinterpret_cast<const float2 *>(e);
-              if (blend_exact<COUNT>(e[1], e[2], mxy.x - xf, mxy.y - yf, sm.exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
+              if (blend_exact<COUNT>(e[1], e[2], mxy.x - xf, mxy.y - yf, exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
                 done = true;
                 smask = 0;
                 if (COUNT) stop_at = base + c0 + kl + 1;
@@ -349,14 +403,14 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
             const float q1 = fmaf(b1.z * dy1, dy1, dx1 * fmaf(b1.x, dx1, (b1.y + b1.y) * dy1));
             const bool s0 = !done && q0 <= b0.w;
             if (__any_sync(0xffffffffu, s0)) {
-              if (s0 && blend_exact<COUNT>(b0, ring[k0 * 3 + 2], dx0, dy0, sm.exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
+              if (s0 && blend_exact<COUNT>(b0, ring[k0 * 3 + 2], dx0, dy0, exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
                 done = true;
                 if (COUNT) stop_at = base + k0 + 1;
               }
             }
             const bool s1 = two && !done && q1 <= b1.w;
             if (__any_sync(0xffffffffu, s1)) {
-              if (s1 && blend_exact<COUNT>(b1, ring[k1 * 3 + 2], dx1, dy1, sm.exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
+              if (s1 && blend_exact<COUNT>(b1, ring[k1 * 3 + 2], dx1, dy1, exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
                 done = true;
                 if (COUNT) stop_at = base + k1 + 1;
               }
@@ -365,6 +419,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
 #endif
           if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
         }
+#endif
         if (warp_done && lane == 0) { atomicAdd(&sm.strip_done[cb], 1u); atomicAdd(&sm.warps_done, 1u); }   // before the release below
       }
       __syncwarp();

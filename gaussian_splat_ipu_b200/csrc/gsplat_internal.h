@@ -140,8 +140,18 @@ static __constant__ unsigned long long EXPF_TAB[32] = {
     0x3feee89f995ad3adull, 0x3feeff76f2fb5e47ull, 0x3fef199bdd85529cull, 0x3fef3720dcef9069ull,
     0x3fef5818dcfba487ull, 0x3fef7c97337b9b5full, 0x3fefa4afa2a490daull, 0x3fefd0765b6e4540ull,
 };
+// table entry k of EXPF_TAB's shared-memory copy; `tab` may be a generic pointer or (TabRef) a 32-bit
+// shared-window address, which spares the generic-to-shared conversion in an inner loop
+struct TabRef { uint32_t saddr; };
+__device__ __forceinline__ unsigned long long exp_tab_entry(const unsigned long long *tab, unsigned long long k) { return tab[k]; }
+__device__ __forceinline__ unsigned long long exp_tab_entry(TabRef tab, unsigned long long k) {
+  unsigned long long v;
+  asm("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(tab.saddr + (uint32_t)k * 8u));
+  return v;
+}
 // the main path of expf: valid for -103.97 < x < 88.72 (no NaN / overflow / underflow handling)
-__device__ __forceinline__ float exp_ref_core(float x, const unsigned long long *tab /* EXPF_TAB in shared memory */) {
+template <typename Tab>
+__device__ __forceinline__ float exp_ref_core(float x, Tab tab /* EXPF_TAB in shared memory */) {
   constexpr double INVLN2N = 0x1.71547652b82fep+0 * 32.0, SHIFT = 0x1.8p+52;
   constexpr double C0 = 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0, C1 = 0x1.ebfce50fac4f3p-3 / 32.0 / 32.0,
                    C2 = 0x1.62e42ff0c52d6p-1 / 32.0;
@@ -151,7 +161,7 @@ __device__ __forceinline__ float exp_ref_core(float x, const unsigned long long 
   const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
   kd = __dsub_rn(kd, SHIFT);
   const double r = __fma_rn(INVLN2N, xd, -kd);
-  const double s = __longlong_as_double((long long)(tab[ki & 31ull] + (ki << 47)));
+  const double s = __longlong_as_double((long long)(exp_tab_entry(tab, ki & 31ull) + (ki << 47)));
   const double zz = __fma_rn(C0, r, C1), r2 = __dmul_rn(r, r);
   double y = __fma_rn(C2, r, 1.0);
   y = __fma_rn(zz, r2, y);
@@ -162,7 +172,7 @@ __device__ __forceinline__ float exp_ref_core(float x, const unsigned long long 
   const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
   kd = __dsub_rn(kd, SHIFT);
   const double r = __dsub_rn(z, kd);
-  const double s = __longlong_as_double((long long)(tab[ki & 31ull] + (ki << 47)));
+  const double s = __longlong_as_double((long long)(exp_tab_entry(tab, ki & 31ull) + (ki << 47)));
   const double zz = __dadd_rn(__dmul_rn(C0, r), C1), r2 = __dmul_rn(r, r);
   double y = __dadd_rn(__dmul_rn(C2, r), 1.0);
   y = __dadd_rn(__dmul_rn(zz, r2), y);

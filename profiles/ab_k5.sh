@@ -2,7 +2,7 @@
 # A/B of K5 builds on the GPU box: frames/s (3 lanes) and the K5 stage time of the 6M @1080p bench frame.
 #   profiles/ab_k5.sh out.txt  name=libpath[:ENV=VAL] ...
 out=$1; shift
-: > "$out"
+mkdir -p "$(dirname "$out")"; : > "$out"
 for spec in "$@"; do
   name=${spec%%=*}; rest=${spec#*=}; lib=${rest%%:*}; envs=""
   [ "$rest" != "$lib" ] && envs=${rest#*:}

@@ -1,18 +1,23 @@
 #!/bin/bash
-# Round-end measurement pass on one B200 (run under gpurun): tests, smoke, both bench arms, then the
-# ncu launch list and one full-set capture of ONE frame (each only after its plain run exited 0).
-mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -q 2>&1 | tail -4 > gpurun_out/t.log; cat gpurun_out/t.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
-timeout 400 python bench.py --stage-report gpurun_out/stage_final.json > gpurun_out/bench_final.json 2> gpurun_out/bench_final.err || exit 1
-timeout 400 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2>> gpurun_out/bench_final.err
-timeout 300 python bench.py --mode multiview --workload synthetic-3M-1080p --steps 5 --warmup 3 > gpurun_out/bench_multiview.json 2>> gpurun_out/bench_final.err
-timeout 300 python bench.py --workload synthetic-1M-1080p --no-cpu-baseline > gpurun_out/bench_1M.json 2>> gpurun_out/bench_final.err
-timeout 300 python bench.py --workload synthetic-6M-4k --no-cpu-baseline --steps 100 > gpurun_out/bench_4k.json 2>> gpurun_out/bench_final.err
-# the captures run ONE frame at a time (one lane, fixed slicing) so that a frame is 57 consecutive launches
-export GSPLAT_SLICE_FRACTIONS=0.08 GSPLAT_CONCURRENT_FRAMES=1
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 1768 --launch-count 130 --csv \
-  --log-file gpurun_out/launches_final.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/ncu1.log 2>&1
-timeout 900 ncu --set full --clock-control none --launch-skip 1768 --launch-count 58 -f -o gpurun_out/prof_frame_final \
-  python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/ncu2.log 2>&1
-ls -la gpurun_out/*.ncu-rep
+# Round-end measurement pass on ONE B200 (run under gpurun): tests, smoke, both bench arms, the other
+# BASELINE configs, then the ncu launch list and one full-set capture of ONE frame (each only after
+# its plain run exited 0).  Output: gpurun_out/final/ (copied into profiles/ by hand, named per round).
+O=gpurun_out/final; mkdir -p $O
+timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -4 > $O/tests.log; cat $O/tests.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+timeout 500 python bench.py --stage-report $O/stages_6M.json > $O/bench_6M.json 2> $O/bench.err || { tail -5 $O/bench.err; exit 1; }
+timeout 400 python bench.py --impl reference --steps 4 --warmup 1 > $O/bench_ref.json 2>> $O/bench.err
+for w in ply-point_cloud_9-720p-div0.1 ply-point_cloud_9-720p-div1.0; do
+  timeout 300 python bench.py --workload $w --steps 100 --warmup 5 >> $O/bench_cfg0.jsonl 2>> $O/bench.err; done
+for w in ply-orbit-720p-div0.1 ply-orbit-720p-div1.0; do
+  timeout 400 python bench.py --workload $w --steps 32 --warmup 3 >> $O/bench_cfg1.jsonl 2>> $O/bench.err; done
+timeout 300 python bench.py --workload synthetic-1M-1080p > $O/bench_cfg2_1M.json 2>> $O/bench.err
+timeout 400 python bench.py --workload synthetic-6M-4k --steps 100 > $O/bench_cfg3_4k_views.json 2>> $O/bench.err
+timeout 300 python bench.py --mode bands --workload synthetic-6M-4k --steps 120 > $O/bench_cfg3_4k_bands_n1.json 2>> $O/bench.err
+timeout 300 python bench.py --mode multiview --workload synthetic-3M-1080p --steps 5 --warmup 3 > $O/bench_cfg4_multiview_n1.json 2>> $O/bench.err
+timeout 200 python profiles/tile_profile.py synthetic-6M-1080p 3 > $O/tile_profile_6M.txt 2>&1
+# the captures run ONE frame at a time (one lane, fixed slicing): profiles/frames.py
+python profiles/frames.py > $O/frames.log 2>&1 || { tail -5 $O/frames.log; exit 1; }
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches.csv python profiles/frames.py > $O/ncu1.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -f -o $O/prof_frame python profiles/frames.py synthetic-6M-1080p 3 > $O/ncu2.log 2>&1
+ls -la $O
