@@ -19,5 +19,5 @@ timeout 200 python profiles/tile_profile.py synthetic-6M-1080p 3 > $O/tile_profi
 # the captures run ONE frame at a time (one lane, fixed slicing): profiles/frames.py
 python profiles/frames.py > $O/frames.log 2>&1 || { tail -5 $O/frames.log; exit 1; }
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches.csv python profiles/frames.py > $O/ncu1.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -f -o $O/prof_frame python profiles/frames.py synthetic-6M-1080p 3 > $O/ncu2.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -f -o $O/prof_frame python profiles/frames.py synthetic-6M-1080p 2 > $O/ncu2.log 2>&1
 ls -la $O
