@@ -119,17 +119,13 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
       R.c[0][0] = 1.f - 2.f * (qyy + qzz); R.c[0][1] = 2.f * (qxy + qwz); R.c[0][2] = 2.f * (qxz - qwy);
       R.c[1][0] = 2.f * (qxy - qwz); R.c[1][1] = 1.f - 2.f * (qxx + qzz); R.c[1][2] = 2.f * (qyz + qwx);
       R.c[2][0] = 2.f * (qxz + qwy); R.c[2][1] = 2.f * (qyz - qwx); R.c[2][2] = 1.f - 2.f * (qxx + qyy);
-      // S = diag(exp(scale)); cov3 = ((R S) S^T) R^T as glm evaluates it.  A product with the diagonal S
-      // has ONE non-zero term per entry: glm's other two are x * 0 = +-0, and adding +-0 changes no
-      // non-zero (finite) sum, so each entry is that single product — the value the host computes
-      // (only the sign of an exact zero can differ, which no later sum or comparison sees).
-      const float sd[3] = {exp_ref(sc0, exp_tab), exp_ref(sc1, exp_tab), exp_ref(sc2, exp_tab)};
-      M3 RSS;
+      M3 S;
 #pragma unroll
       for (int c = 0; c < 3; ++c)
 #pragma unroll
-        for (int k = 0; k < 3; ++k) RSS.c[c][k] = (R.c[c][k] * sd[c]) * sd[c];
-      const M3 cov3 = m3_mul(RSS, m3_t(R));
+        for (int k = 0; k < 3; ++k) S.c[c][k] = 0.f;
+      S.c[0][0] = exp_ref(sc0, exp_tab); S.c[1][1] = exp_ref(sc1, exp_tab); S.c[2][2] = exp_ref(sc2, exp_tab);
+      const M3 cov3 = m3_mul(m3_mul(m3_mul(R, S), m3_t(S)), m3_t(R));
 
       // ---- Gaussian3D::ComputeCov2D, ipu_geometry.hpp:333-383.  mv is the FULL projection*view
       // product and tan_fovy == tan_fovx (reference quirks, kept): t == clip.
@@ -139,17 +135,16 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
       const float txtz = tx / tz, tytz = ty / tz;
       tx = min_ref(lim, max_ref(-lim, txtz)) * tz;
       ty = min_ref(lim, max_ref(-lim, tytz)) * tz;
-      // J (glm column-major ctor, ipu_geometry.hpp:345-348) = columns (jx, 0, jxz), (0, jy, jyz), (0, 0, 0);
-      // T = W J: again the products with J's exact zeros only add +-0
-      const float jx = fp.focal_x / tz, jxz = -(fp.focal_x * tx) / (tz * tz);
-      const float jy = fp.focal_y / tz, jyz = -(fp.focal_y * ty) / (tz * tz);
-      M3 T;
+      M3 J;
+      J.c[0][0] = fp.focal_x / tz; J.c[0][1] = 0.0f; J.c[0][2] = -(fp.focal_x * tx) / (tz * tz);
+      J.c[1][0] = 0.0f; J.c[1][1] = fp.focal_y / tz; J.c[1][2] = -(fp.focal_y * ty) / (tz * tz);
+      J.c[2][0] = 0.f; J.c[2][1] = 0.f; J.c[2][2] = 0.f;
+      M3 Wm;
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        T.c[0][k] = m[0 * 4 + k] * jx + m[2 * 4 + k] * jxz;
-        T.c[1][k] = m[1 * 4 + k] * jy + m[2 * 4 + k] * jyz;
-        T.c[2][k] = 0.f;
-      }
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) Wm.c[c][k] = m[c * 4 + k];
+      const M3 T = m3_mul(Wm, J);
       M3 cov = m3_mul(m3_mul(m3_t(T), m3_t(cov3)), T);
       cov.c[0][0] += 0.3f;
       cov.c[1][1] += 0.3f;

@@ -15,6 +15,6 @@ python profiles/frame_launches.py $F/launches.csv > profiles/launches_$R.txt
 python profiles/summarize_ncu.py launches $F/launches.csv > profiles/launches_all_$R.txt
 python profiles/summarize_ncu.py report $F/prof_frame.ncu-rep > profiles/prof_frame_$R.txt
 python profiles/traffic_frame.py $F/prof_frame.ncu-rep > profiles/traffic_$R.json
-{ python profiles/stalls.py $F/prof_frame.ncu-rep blend_kernel 0 30; python profiles/stalls.py $F/prof_frame.ncu-rep blend_kernel 1 12;
-  python profiles/sass_mix.py $F/prof_frame.ncu-rep blend_kernel 0; } > profiles/prof_blend_$R.txt 2>&1
+{ python profiles/stalls.py $F/prof_blend.ncu-rep blend_kernel 0 30; python profiles/stalls.py $F/prof_blend.ncu-rep blend_kernel 1 12;
+  python profiles/sass_mix.py $F/prof_blend.ncu-rep blend_kernel 0; } > profiles/prof_blend_$R.txt 2>&1
 ls -la profiles/*_$R.*

@@ -19,5 +19,8 @@ timeout 200 python profiles/tile_profile.py synthetic-6M-1080p 3 > $O/tile_profi
 # the captures run ONE frame at a time (one lane, fixed slicing): profiles/frames.py
 python profiles/frames.py > $O/frames.log 2>&1 || { tail -5 $O/frames.log; exit 1; }
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches.csv python profiles/frames.py > $O/ncu1.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -f -o $O/prof_frame python profiles/frames.py synthetic-6M-1080p 2 > $O/ncu2.log 2>&1
+# one frame (57 launches) + the next frame's K1, every section; then K5 alone with its source for the stall sites.
+# gpurun brings back at most 64 MiB: no --import-source on the whole-frame capture
+timeout 900 ncu --set full --clock-control none --launch-skip 58 --launch-count 58 -f -o $O/prof_frame python profiles/frames.py synthetic-6M-1080p 3 > $O/ncu2.log 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:blend_kernel --launch-skip 2 --launch-count 2 -f -o $O/prof_blend python profiles/frames.py synthetic-6M-1080p 3 > $O/ncu3.log 2>&1
 ls -la $O
