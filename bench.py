@@ -62,7 +62,9 @@ class Scene:
     def __init__(self, name, g, views, proj, W, H, scale_div, views_note, l2_note, data):
         self.name, self.g, self.views, self.proj, self.W, self.H = name, g, views, proj, W, H
         self.scale_div, self.views_note, self.l2_note, self.data = scale_div, views_note, l2_note, data
-        self.small = g.shape[0] * 116 < 126e6      # scene + records fit the 126 MB L2
+        # "small": scene (56 B) + one lane's records and keys (60 B) per Gaussian fit the 126 MB L2 with room to
+        # spare; from 0.5 M Gaussians on the three lanes' working sets (56 + 3 * 60 B each) exceed it
+        self.small = g.shape[0] < 500_000
 
     def config(self):
         """The `config` object of the JSON line: identical for the b200 and the reference arm."""
@@ -597,6 +599,8 @@ def ply_orbit_arm(args):
             s.updateModelView(v)
             s.timer_begin(); s.execute(); ms += s.timer_end()
         launches += launch_count() - l0
+        for v in scn.views[:2 * s.concurrent_frames + 1]:      # first use of the stream allocates its pinned slots
+            s.updateModelView(v); s.acquireFrame(s.executeStreamed())
         t0 = time.perf_counter()                 # e2e: the frame stream over the same orbit (L2 not flushed)
         inflight = []
         for v in scn.views:
