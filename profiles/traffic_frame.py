@@ -11,7 +11,7 @@ ik, ir, iw, it = (hdr.index(k) for k in ("Kernel Name", "dram__bytes_read.sum", 
 # hardware-side view of each kernel (bench.py copies the dominant stage's into roofline.ncu)
 PIPE = {"fma_pipe_pct": "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
         "fp64_pipe_pct": "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
-        "issue_active_pct": "sm__issue_active.avg.pct_of_peak_sustained_active",
+        "issue_active_pct": "sm__inst_issued.avg.pct_of_peak_sustained_active",
         "threads_per_inst": "smsp__thread_inst_executed_per_inst_executed.ratio",
         "warps_active_pct": "sm__warps_active.avg.pct_of_peak_sustained_active",
         "dram_throughput_pct": "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
