@@ -62,15 +62,22 @@ constexpr int BLEND_MAX_WARPS = 20;                  // consumer warps of an und
 #ifndef GSPLAT_BLEND_TMA
 #define GSPLAT_BLEND_TMA 0
 #endif
-// Inner loop: 1 = per-pixel entry sets (phase A pre-test per entry, phase B exact chain per lane),
-// 0 = entry by entry (each surviving entry runs the exact chain for the lanes it reaches).
-#ifndef GSPLAT_BLEND_LANELIST
-#define GSPLAT_BLEND_LANELIST 1
+// Measured and dropped (profiles/ab_k5_r2.txt): the entry-by-entry inner loop (each surviving entry
+// runs the exact chain for the lanes it reaches: 4 % slower than the per-pixel sets below) and 64
+// staged entries per consumer turn (one phase B over two chunks: K5 0.373-0.379 ms against 0.348-0.350).
+// 1 = phase A walks a compacted list of the hit lanes, 0 = find-first-set on the hit ballot.
+// Measured (profiles/ab_k5_r3a.txt): the list is SLOWER, K5 0.331 ms against 0.314 (the store, the warp
+// barrier and the dependent load cost more than the uniform-datapath bit walk): default 0.
+#ifndef GSPLAT_BLEND_HITLIST
+#define GSPLAT_BLEND_HITLIST 0
 #endif
-// staged entries a consumer warp takes per turn of its loop (32 or 64; 64 needs the per-pixel sets).
-// Measured (profiles/ab_k5_r2.txt): 64 is SLOWER (K5 0.373-0.379 ms against 0.348-0.350): keep 32.
-#ifndef GSPLAT_BLEND_SPAN
-#define GSPLAT_BLEND_SPAN 32
+// 1 = phase B's turn is straight-line (selects), 0 = branches per test (measured: 0.331 against 0.361 ms)
+#ifndef GSPLAT_BLEND_PRED
+#define GSPLAT_BLEND_PRED 1
+#endif
+// 1 = keep expf's f64 constants and the table address in registers across the blend loop (0.331 against 0.341 ms)
+#ifndef GSPLAT_BLEND_HOIST
+#define GSPLAT_BLEND_HOIST 1
 #endif
 constexpr uint32_t BLEND_FULL_ARRIVALS = GSPLAT_BLEND_TMA ? 1u : 32u;   // arrivals that complete a "full" phase
 
@@ -79,6 +86,7 @@ struct BlendSmem {
   unsigned long long full[BLEND_STAGES];             // mbarrier: the stage's bytes have landed
   unsigned long long empty[BLEND_STAGES];            // mbarrier: every consumer warp is done with the stage
   unsigned long long exp_tab[32];                    // exp_ref's 2^(k/32) table
+  uint32_t hits[BLEND_MAX_WARPS][34];                // per consumer warp: lanes of the chunk's hit entries, in order
   uint32_t warps_done;                               // consumer warps whose 32 pixels have all stopped
   uint32_t strip_done[4];                            // the same per 8-pixel column strip of the part
   uint32_t stop;                                     // producer: nothing more will be staged
@@ -95,11 +103,34 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long *bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
 }
-// Blocks until the phase of `bar` with the given parity has completed.  try_wait suspends the thread
-// in hardware for up to the time hint (ns) and returns early when the phase completes, so the long
-// hint costs no latency; without it the loop re-issues every few hundred cycles and a CTA's idle
-// producer warp alone burned 12 % of K5's issue slots spinning (profiles/prof_blend_r2a.txt).
+// Blocks until the phase of `bar` with the given parity has completed.
+//   GSPLAT_BLEND_WAIT_NS = 0: try_wait with a suspend-time hint (GSPLAT_BLEND_WAIT_HINT ns): the thread
+//     is suspended in hardware until the phase completes or the hint runs out.
+//   GSPLAT_BLEND_WAIT_NS > 0: plain try_wait, then nanosleep of that many ns before the next try: a
+//     waiting warp issues a handful of instructions per sleep instead of re-polling (measured in the
+//     round-2 capture: 13 % of K5's warp instructions were re-polls of the hinted form, ~90 per wait).
+#ifndef GSPLAT_BLEND_WAIT_NS
+#define GSPLAT_BLEND_WAIT_NS 0
+#endif
+#ifndef GSPLAT_BLEND_WAIT_HINT
+#define GSPLAT_BLEND_WAIT_HINT 0x989680
+#endif
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity) {
+#if GSPLAT_BLEND_WAIT_NS > 0
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "WAIT_%=:\n"
+      "nanosleep.u32 %2;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@!p bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_addr(bar)),
+      "r"(parity), "r"((uint32_t)GSPLAT_BLEND_WAIT_NS)
+      : "memory");
+#else
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
@@ -109,8 +140,9 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t pari
       "bra WAIT_%=;\n"
       "DONE_%=:\n"
       "}\n" ::"r"(smem_addr(bar)),
-      "r"(parity), "r"(0x989680u)
+      "r"(parity), "r"((uint32_t)GSPLAT_BLEND_WAIT_HINT)
       : "memory");
+#endif
 }
 // 48-byte global -> shared bulk copy, completion signalled on `bar` in bytes (complete_tx)
 __device__ __forceinline__ void bulk_copy_48(void *dst, const void *src, unsigned long long *bar) {
@@ -138,13 +170,13 @@ __device__ __forceinline__ uint32_t ld_volatile_shared(const uint32_t *p) {
 // codelets.cpp:389-410; returns true when the pixel stops at this entry.
 template <bool COUNT>
 __device__ __forceinline__ bool blend_exact(const float4 b, const float4 c, float dx, float dy,
-                                            const TabRef exp_tab, float &T, float &Cr, float &Cg,
-                                            float &Cb, float &Ca, unsigned long long &n_blend) {
+                                            const TabRef exp_tab, const ExpConsts &ek, float &T, float &Cr,
+                                            float &Cg, float &Cb, float &Ca, unsigned long long &n_blend) {
   const float power = -0.5f * (b.x * dx * dx + b.z * dy * dy) - b.y * dx * dy;
   if (power > 0.0f) return false;
   // survivors of the pre-test have -13 < power <= 0: exp_ref's NaN / overflow / underflow branches
   // cannot be taken and are skipped
-  const float e = c.x * exp_ref_core(power, exp_tab);
+  const float e = c.x * exp_ref_core(power, exp_tab, ek);
   const float alpha = e < 0.99f ? e : 0.99f;        // glm::min(0.99f, e)
   if (alpha < ALPHA_MIN) return false;
   const float test_T = T * (1.f - alpha);
@@ -158,6 +190,30 @@ __device__ __forceinline__ bool blend_exact(const float4 b, const float4 c, floa
   return false;
 }
 
+// The same step as straight-line code: `on` false leaves the pixel untouched whatever the entry
+// holds (a lane without work is handed a stale ring entry).  Same operations on the same values in
+// the same order for the lanes that are on, so the results are those of blend_exact bit for bit.
+template <bool COUNT>
+__device__ __forceinline__ bool blend_exact_pred(bool on, const float4 b, const float4 c, float dx, float dy,
+                                                 const TabRef exp_tab, const ExpConsts &ek, float &T, float &Cr,
+                                                 float &Cg, float &Cb, float &Ca, unsigned long long &n_blend) {
+  const float power = -0.5f * (b.x * dx * dx + b.z * dy * dy) - b.y * dx * dy;
+  const float e = c.x * exp_ref_core(power, exp_tab, ek);
+  const float alpha = e < 0.99f ? e : 0.99f;
+  const float test_T = T * (1.f - alpha);
+  const bool ok = on && !(power > 0.0f) && !(alpha < ALPHA_MIN);
+  const bool stop = ok && test_T < 0.0001f;
+  const bool upd = ok && !stop;
+  const float ar = c.y * alpha * T, ag = c.z * alpha * T, ab = c.w * alpha * T, aa = c.x * alpha * T;
+  Cr = upd ? Cr + ar : Cr;
+  Cg = upd ? Cg + ag : Cg;
+  Cb = upd ? Cb + ab : Cb;
+  Ca = upd ? Ca + aa : Ca;
+  T = upd ? test_T : T;
+  if (COUNT) n_blend += upd ? 1ull : 0ull;
+  return stop;
+}
+
 // Depth slices (see duplicate.cu): the list of a tile may arrive in several consecutive pieces, one
 // launch each.  Between launches a pixel's state lives in the framebuffer (C) and in `tstate`
 // (T, or -1 once the pixel has stopped); a tile whose pixels have all stopped raises
@@ -167,7 +223,7 @@ __device__ __forceinline__ bool blend_exact(const float4 b, const float4 c, floa
 template <bool COUNT, bool FIRST, bool LAST>
 __global__ void __launch_bounds__((BLEND_MAX_WARPS + 1) * 32)
 blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
-             int tiles_across, const uint32_t *__restrict__ band, int full_tile_h, int part_w, float4 *__restrict__ fb,
+             int tiles_across, const uint32_t *__restrict__ band, int full_tile_h, int split_log2, float4 *__restrict__ fb,
              float *__restrict__ tstate, TileState ts, const uint32_t *__restrict__ order,
              unsigned long long *__restrict__ pair_counters) {
   extern __shared__ __align__(128) unsigned char blend_smem_raw[];
@@ -175,28 +231,44 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   const long long t_begin = COUNT ? clock64() : 0;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t NW = (blockDim.x >> 5) - 1;           // consumer warps
-  // a CTA blends a "part" of a semantic tile: all its rows, `part_w` = 32 / nsub of its columns (the
-  // whole tile, or a column strip so that a crowded tile's list is walked by several SMs at
+  // a CTA blends a "part" of a semantic tile: all its rows, `part_w` = 32 >> split_log2 of its columns
+  // (the whole tile, or a column strip so that a crowded tile's list is walked by several SMs at
   // once); parts of one tile are neighbours in the grid.  A warp owns an 8 x 4 pixel block: a splat
   // a few pixels across then occupies a third of the lanes of the warps it reaches, where a
-  // 32 x 1 pixel row would leave nine lanes in ten idle.
-  const uint32_t nsub = (uint32_t)(32 / part_w), sub = blockIdx.x % nsub;
+  // 32 x 1 pixel row would leave nine lanes in ten idle.  (Shifts and masks only: this prologue is
+  // run by every warp of every CTA, two thirds of which find an empty list on the bench frame.)
+  const uint32_t sl = (uint32_t)split_log2, part_w = 32u >> sl, sub = blockIdx.x & ((1u << sl) - 1u);
+  const uint32_t slot = blockIdx.x >> sl;
   // the grid covers the whole image; this context's band (device words written by K1) may be less
   const uint32_t row_begin = band[0], row_end = band[1];
-  if (blockIdx.x / nsub >= (row_end - row_begin) * (uint32_t)tiles_across) return;
-  // tiles are taken longest list first (tile_order_kernel) so the long ones do not start last
-  const uint32_t tile = order[blockIdx.x / nsub] + row_begin * (uint32_t)tiles_across;
+  if (slot >= (row_end - row_begin) * (uint32_t)tiles_across) return;
+  // tiles are taken longest list first (tile_order_kernel, which hands out (row, column) of the
+  // band's tiles packed in one word) so the long ones do not start last
+  const uint32_t packed = order[slot];
+  const uint32_t tcol = packed & 0xffffu, trow = row_begin + (packed >> 16);
+  const uint32_t tile = trow * (uint32_t)tiles_across + tcol;
   const uint2 range = ranges[tile];
   const uint32_t n = range.y - range.x;
   // "done" flags are kept per 8-pixel column STRIP of the tile (4 per tile) so that slices may cut
   // the tile into different numbers of parts (the later, emptier slices use narrower parts)
-  const uint32_t strips = (uint32_t)part_w / 8u, strip0 = tile * 4u + sub * strips;
-  if (!FIRST) {
-    bool all_done = n == 0;                               // nothing new for this part: its state stands
-    if (!all_done) {
-      all_done = true;
-      for (uint32_t k = 0; k < strips; ++k) all_done = all_done && ts.part_done[strip0 + k];
+  const uint32_t strips = part_w >> 3, strip0 = tile * 4u + sub * strips;
+  // consumer geometry: this warp's 8 x 4 block and this lane's pixel
+  const uint32_t cb = warp & (strips - 1u), rb = warp >> (2u - sl);
+  const uint32_t x_local = sub * part_w + cb * 8u + (lane & 7u), y_local = rb * 4u + (lane >> 3);
+  const bool valid = y_local < (uint32_t)full_tile_h;    // tile heights that are no multiple of 4
+  // a10 layout: tile-major, row-major inside the tile
+  const size_t px = (size_t)tile * (32 * full_tile_h) + (size_t)(valid ? y_local : 0u) * 32 + x_local;
+  if (n == 0) {
+    // nothing (new) in this part's list.  First slice: the pixels' initial state is the result.
+    if (FIRST && warp != NW && valid) {
+      fb[px] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!LAST) tstate[px] = 1.f;
     }
+    return;
+  }
+  if (!FIRST) {
+    bool all_done = true;                                 // every pixel of the part has stopped: its state stands
+    for (uint32_t k = 0; k < strips; ++k) all_done = all_done && ts.part_done[strip0 + k];
     if (all_done) return;
   }
 
@@ -211,7 +283,6 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   __syncthreads();
 
   const uint32_t nbatch = (n + BLEND_BATCH - 1) / BLEND_BATCH;
-  const uint32_t tcol = tile % tiles_across, trow = tile / tiles_across;
 
   if (warp == NW) {
     // ---- producer: the tile's list, BLEND_BATCH entries per stage --------------------------------
@@ -262,19 +333,27 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
     }
   } else {
     // ---- consumers ---------------------------------------------------------------------------
-    const uint32_t cbn = (uint32_t)part_w / 8u;            // 8-pixel column blocks per part
-    const uint32_t cb = warp % cbn, rb = warp / cbn;       // this warp's block
-    const uint32_t x_local = sub * (uint32_t)part_w + cb * 8u + (lane & 7u), y_local = rb * 4u + (lane >> 3);
-    const bool valid = y_local < (uint32_t)full_tile_h;    // tile heights that are no multiple of 4
-    // a10 layout: tile-major, row-major inside the tile
-    const size_t px = (size_t)tile * (32 * full_tile_h) + (size_t)(valid ? y_local : 0u) * 32 + x_local;
     const float xf = (float)(tcol * 32u + x_local);
     const float yf = (float)(trow * full_tile_h) + (float)y_local;
     // centre of the warp's 8 x 4 block (pixels x0..x0+7, y0..y0+3)
-    const float bcx = (float)(tcol * 32u + sub * (uint32_t)part_w + cb * 8u) + 3.5f;
+    const float bcx = (float)(tcol * 32u + sub * part_w + cb * 8u) + 3.5f;
     const float bcy = (float)(trow * full_tile_h + rb * 4u) + 1.5f;
 
+#if GSPLAT_BLEND_HOIST
+    // loop invariants the compiler would otherwise rebuild on every trip of the blend loop
+    uint32_t exp_tab_addr = smem_addr(sm.exp_tab);
+    asm volatile("" : "+r"(exp_tab_addr));
+    const TabRef exp_tab{exp_tab_addr};
+    const ExpConsts ek = exp_consts(true);
+#else
     const TabRef exp_tab{smem_addr(sm.exp_tab)};
+    const ExpConsts ek = exp_consts(false);
+#endif
+#if GSPLAT_BLEND_HITLIST
+    uint32_t *my_hits = sm.hits[warp];
+    uint32_t lanemask_lt;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(lanemask_lt));
+#endif
     float T = 1.f, Cr = 0.f, Cg = 0.f, Cb = 0.f, Ca = 0.f;
     bool done = !valid;
     if (!FIRST && valid) {
@@ -295,54 +374,6 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       if (!warp_done) {
         const uint32_t base = it * BLEND_BATCH, cnt = min((uint32_t)BLEND_BATCH, n - base);
         const float4 *ring = sm.ring[stage];
-#if GSPLAT_BLEND_LANELIST && GSPLAT_BLEND_SPAN == 64
-        // 64 staged entries per turn: two hit ballots, phase A over both, ONE phase B over the union —
-        // the longest per-pixel set of 64 entries is relatively shorter than of 32 (more lanes busy)
-        for (uint32_t c0 = 0; c0 < cnt; c0 += 64) {
-          uint32_t smask[2] = {0u, 0u};
-#pragma unroll
-          for (uint32_t h = 0; h < 2; ++h) {
-            const uint32_t jj = c0 + h * 32 + lane;
-            bool hit = false;
-            if (jj < cnt) {
-              const float4 a = ring[jj * 3];
-              hit = fabsf(a.x - bcx) <= a.z + 3.5f && fabsf(a.y - bcy) <= a.w + 1.5f;
-            }
-            uint32_t mask = __ballot_sync(0xffffffffu, hit);
-            const uint32_t cb0 = c0 + h * 32;
-            uint32_t sm_ = 0;
-            while (mask) {
-              const uint32_t l0 = __ffs(mask) - 1;
-              mask &= mask - 1;
-              const bool two = mask != 0;
-              const uint32_t l1 = two ? __ffs(mask) - 1 : l0;
-              mask &= mask - 1;
-              const float4 a0 = ring[(cb0 + l0) * 3], b0 = ring[(cb0 + l0) * 3 + 1];
-              const float4 a1 = ring[(cb0 + l1) * 3], b1 = ring[(cb0 + l1) * 3 + 1];
-              const float dx0 = a0.x - xf, dy0 = a0.y - yf, dx1 = a1.x - xf, dy1 = a1.y - yf;
-              const float q0 = fmaf(b0.z * dy0, dy0, dx0 * fmaf(b0.x, dx0, (b0.y + b0.y) * dy0));
-              const float q1 = fmaf(b1.z * dy1, dy1, dx1 * fmaf(b1.x, dx1, (b1.y + b1.y) * dy1));
-              sm_ |= (q0 <= b0.w ? 1u << l0 : 0u) | (two && q1 <= b1.w ? 1u << l1 : 0u);
-            }
-            smask[h] = done ? 0u : sm_;
-          }
-          unsigned long long todo = (unsigned long long)smask[0] | ((unsigned long long)smask[1] << 32);
-          while (__any_sync(0xffffffffu, todo != 0ull)) {
-            if (todo) {
-              const uint32_t k = c0 + (uint32_t)__ffsll((long long)todo) - 1u;
-              todo &= todo - 1ull;
-              const float4 *e = ring + k * 3;
-              const float2 mxy = *reinterpret_cast<const float2 *>(e);
-              if (blend_exact<COUNT>(e[1], e[2], mxy.x - xf, mxy.y - yf, exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
-                done = true;
-                todo = 0ull;
-                if (COUNT) stop_at = base + k + 1;
-              }
-            }
-          }
-          if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
-        }
-#else
         for (uint32_t c0 = 0; c0 < cnt; c0 += 32) {
           // lane = entry: does the box around its alpha >= 1/255 ellipse reach this warp's block?
           const uint32_t jj = c0 + lane;
@@ -352,74 +383,72 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
             hit = fabsf(a.x - bcx) <= a.z + 3.5f && fabsf(a.y - bcy) <= a.w + 1.5f;
           }
           uint32_t mask = __ballot_sync(0xffffffffu, hit);
-#if GSPLAT_BLEND_LANELIST
           // Phase A, whole warp per entry: the fused pre-test q = A dx^2 + 2 B dx dy + C dy^2 against
           // qmax (alpha < 1/255 beyond it) gives every pixel the set of chunk entries it must blend.
+          // Two entries per turn (their loads and pre-tests overlap).
           uint32_t smask = 0;
+#if GSPLAT_BLEND_HITLIST
+          // the hit lanes write their lane numbers, in order, to the warp's list: the walk below is an
+          // indexed loop (one 8-byte load per two entries) instead of find-first-set on the ballot
+          const uint32_t nh = __popc(mask);
+          if (hit) {
+            const uint32_t pos = __popc(mask & lanemask_lt);
+            my_hits[pos] = lane;
+            if (pos + 1 == nh) my_hits[nh] = lane;          // an odd count walks its last entry twice
+          }
+          __syncwarp();
+          for (uint32_t i = 0; i < nh; i += 2) {
+            const uint2 ll = *reinterpret_cast<const uint2 *>(my_hits + i);
+            const uint32_t l0 = ll.x, l1 = ll.y;
+#else
           while (mask) {
             const uint32_t l0 = __ffs(mask) - 1;
             mask &= mask - 1;
-            const bool two = mask != 0;
-            const uint32_t l1 = two ? __ffs(mask) - 1 : l0;
+            const uint32_t l1 = mask ? __ffs(mask) - 1 : l0;
             mask &= mask - 1;
+#endif
             const float4 a0 = ring[(c0 + l0) * 3], b0 = ring[(c0 + l0) * 3 + 1];
             const float4 a1 = ring[(c0 + l1) * 3], b1 = ring[(c0 + l1) * 3 + 1];
             const float dx0 = a0.x - xf, dy0 = a0.y - yf, dx1 = a1.x - xf, dy1 = a1.y - yf;
             const float q0 = fmaf(b0.z * dy0, dy0, dx0 * fmaf(b0.x, dx0, (b0.y + b0.y) * dy0));
             const float q1 = fmaf(b1.z * dy1, dy1, dx1 * fmaf(b1.x, dx1, (b1.y + b1.y) * dy1));
-            smask |= (q0 <= b0.w ? 1u << l0 : 0u) | (two && q1 <= b1.w ? 1u << l1 : 0u);
+            smask |= (q0 <= b0.w ? 1u << l0 : 0u) | (q1 <= b1.w ? 1u << l1 : 0u);
           }
           if (done) smask = 0;
           // Phase B, one pixel per lane: every lane walks ITS OWN entries in list order through the
           // exact chain, so a turn of the loop blends up to 32 different (pixel, entry) pairs instead of
           // one entry against the few pixels it reaches; turns = the longest per-pixel set.
           while (__any_sync(0xffffffffu, smask != 0)) {
+#if GSPLAT_BLEND_PRED
+            // straight-line turn: lanes whose set is empty run a stale entry with `on` false.  With
+            // ~15 lanes busy per turn (measured) a warp-level skip almost never happens, and the
+            // branches + reconvergence points cost more issue slots than they save.
+            const bool on = smask != 0;
+            const uint32_t kl = (uint32_t)(__ffs(smask) - 1) & 31u;
+            smask &= smask - 1;
+            const float4 *e = ring + (c0 + kl) * 3;
+            const float2 mxy = *reinterpret_cast<const float2 *>(e);
+            if (blend_exact_pred<COUNT>(on, e[1], e[2], mxy.x - xf, mxy.y - yf, exp_tab, ek, T, Cr, Cg, Cb, Ca, n_blend)) {
+              done = true;
+              smask = 0;
+              if (COUNT) stop_at = base + c0 + kl + 1;
+            }
+#else
             if (smask) {
               const uint32_t kl = __ffs(smask) - 1;
               smask &= smask - 1;
               const float4 *e = ring + (c0 + kl) * 3;
               const float2 mxy = *reinterpret_cast<const float2 *>(e);
-              if (blend_exact<COUNT>(e[1], e[2], mxy.x - xf, mxy.y - yf, exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
+              if (blend_exact<COUNT>(e[1], e[2], mxy.x - xf, mxy.y - yf, exp_tab, ek, T, Cr, Cg, Cb, Ca, n_blend)) {
                 done = true;
                 smask = 0;
                 if (COUNT) stop_at = base + c0 + kl + 1;
               }
             }
-          }
-#else
-          // two list entries per turn: their loads and fused pre-tests overlap; they are then applied
-          // to the pixel strictly in list order
-          while (mask) {
-            const uint32_t k0 = c0 + __ffs(mask) - 1;
-            mask &= mask - 1;
-            const bool two = mask != 0;
-            const uint32_t k1 = two ? c0 + __ffs(mask) - 1 : k0;
-            mask &= mask - 1;
-            const float4 a0 = ring[k0 * 3], b0 = ring[k0 * 3 + 1];
-            const float4 a1 = ring[k1 * 3], b1 = ring[k1 * 3 + 1];
-            const float dx0 = a0.x - xf, dy0 = a0.y - yf, dx1 = a1.x - xf, dy1 = a1.y - yf;
-            // fused pre-test: q = A dx^2 + 2 B dx dy + C dy^2 against qmax (alpha < 1/255 beyond it)
-            const float q0 = fmaf(b0.z * dy0, dy0, dx0 * fmaf(b0.x, dx0, (b0.y + b0.y) * dy0));
-            const float q1 = fmaf(b1.z * dy1, dy1, dx1 * fmaf(b1.x, dx1, (b1.y + b1.y) * dy1));
-            const bool s0 = !done && q0 <= b0.w;
-            if (__any_sync(0xffffffffu, s0)) {
-              if (s0 && blend_exact<COUNT>(b0, ring[k0 * 3 + 2], dx0, dy0, exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
-                done = true;
-                if (COUNT) stop_at = base + k0 + 1;
-              }
-            }
-            const bool s1 = two && !done && q1 <= b1.w;
-            if (__any_sync(0xffffffffu, s1)) {
-              if (s1 && blend_exact<COUNT>(b1, ring[k1 * 3 + 2], dx1, dy1, exp_tab, T, Cr, Cg, Cb, Ca, n_blend)) {
-                done = true;
-                if (COUNT) stop_at = base + k1 + 1;
-              }
-            }
-          }
 #endif
+          }
           if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
         }
-#endif
         if (warp_done && lane == 0) { atomicAdd(&sm.strip_done[cb], 1u); atomicAdd(&sm.warps_done, 1u); }   // before the release below
       }
       __syncwarp();
@@ -444,7 +473,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   }
   if (!LAST) {
     __syncthreads();   // every consumer warp has added itself to the counters if its pixels have stopped
-    const uint32_t row_blocks = NW / strips;
+    const uint32_t row_blocks = NW >> (2u - sl);
     if (tid < strips && sm.strip_done[tid] == row_blocks && !ts.part_done[strip0 + tid]) {
       ts.part_done[strip0 + tid] = 1;
       if (atomicAdd(&ts.parts_done[tile], 1u) + 1u == 4u) ts.tile_done[tile] = 1;   // last strip of the tile to stop
@@ -456,8 +485,9 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
 // CTAs are dispatched in blockIdx order; a tile with a long list that starts late leaves the other
 // SMs idle at the end of the launch.  One CTA buckets the band's tiles by list length (power-of-two
 // class + 2 mantissa bits, longest class first; tiles that already stopped count as empty) and
-// writes the permutation K5 indexes with blockIdx.  Order inside a class is arbitrary: it only
-// changes scheduling, never results.
+// writes the permutation K5 indexes with blockIdx, each tile as (row within the band) << 16 | column
+// so that K5's prologue needs no division.  Order inside a class is arbitrary: it only changes
+// scheduling, never results.
 constexpr int ORDER_BUCKETS = 33 * 4;
 __device__ __forceinline__ uint32_t order_bucket(uint32_t len) {
   if (len == 0) return ORDER_BUCKETS - 1;
@@ -507,7 +537,7 @@ tile_order_kernel(const uint2 *__restrict__ ranges, int tiles_across, const uint
   for (int i = threadIdx.x; i < ntiles; i += blockDim.x) {
     const uint2 r = ranges[t0 + i];
     const uint32_t len = (tile_done && tile_done[t0 + i]) ? 0u : r.y - r.x;
-    order[atomicAdd(&cnt[order_bucket(len)], 1u)] = (uint32_t)i;
+    order[atomicAdd(&cnt[order_bucket(len)], 1u)] = ((uint32_t)(i / tiles_across) << 16) | (uint32_t)(i % tiles_across);
   }
 }
 
@@ -523,11 +553,12 @@ static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, cons
                            const uint32_t *order, unsigned long long *pair_counters, cudaStream_t st) {
   const int rows = fp.tiles_down;   // launch geometry for the whole image: the band is only known on the device
   const int full_h = (int)fp.tile_h;
-  const int part_w = 32 / split;                                  // columns per CTA (split is 1, 2 or 4)
+  const int split_log2 = split >= 4 ? 2 : (split >= 2 ? 1 : 0);  // split is 1, 2 or 4
+  const int part_w = 32 >> split_log2;                            // columns per CTA
   const int warps = (part_w / 8) * ((full_h + 3) / 4);           // one consumer warp per 8 x 4 pixel block
   ++g_launches;
-  blend_kernel<COUNT, FIRST, LAST><<<rows * fp.tiles_across * split, (warps + 1) * 32, sizeof(BlendSmem), st>>>(
-      p, sorted_vals, ranges, fp.tiles_across, band, full_h, part_w, fb_tiled, tstate, ts, order, pair_counters);
+  blend_kernel<COUNT, FIRST, LAST><<<(rows * fp.tiles_across) << split_log2, (warps + 1) * 32, sizeof(BlendSmem), st>>>(
+      p, sorted_vals, ranges, fp.tiles_across, band, full_h, split_log2, fb_tiled, tstate, ts, order, pair_counters);
 }
 
 template <bool COUNT, bool FIRST, bool LAST> static cudaError_t blend_attr() {

@@ -149,36 +149,48 @@ __device__ __forceinline__ unsigned long long exp_tab_entry(TabRef tab, unsigned
   asm("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(tab.saddr + (uint32_t)k * 8u));
   return v;
 }
+// exp_ref_core's f64 constants.  exp_consts(true) reads them from constant memory, to be called ONCE
+// outside a hot loop: the values then stay in registers (or become constant-bank operands) across
+// the loop, where literal constants are re-materialised on every trip (8 moves per expf in K5's
+// inner loop, profiles/) — ptxas folds anything whose value it can see.
+struct ExpConsts { double invln2n, c0, c1, c2; };
+static __constant__ double EXPF_K[4] = {0x1.71547652b82fep+0 * 32.0, 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0,
+                                        0x1.ebfce50fac4f3p-3 / 32.0 / 32.0, 0x1.62e42ff0c52d6p-1 / 32.0};
+__device__ __forceinline__ ExpConsts exp_consts(bool from_memory) {
+  if (from_memory) return ExpConsts{EXPF_K[0], EXPF_K[1], EXPF_K[2], EXPF_K[3]};
+  return ExpConsts{0x1.71547652b82fep+0 * 32.0, 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0,
+                   0x1.ebfce50fac4f3p-3 / 32.0 / 32.0, 0x1.62e42ff0c52d6p-1 / 32.0};
+}
 // the main path of expf: valid for -103.97 < x < 88.72 (no NaN / overflow / underflow handling)
 template <typename Tab>
-__device__ __forceinline__ float exp_ref_core(float x, Tab tab /* EXPF_TAB in shared memory */) {
-  constexpr double INVLN2N = 0x1.71547652b82fep+0 * 32.0, SHIFT = 0x1.8p+52;
-  constexpr double C0 = 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0, C1 = 0x1.ebfce50fac4f3p-3 / 32.0 / 32.0,
-                   C2 = 0x1.62e42ff0c52d6p-1 / 32.0;
+__device__ __forceinline__ float exp_ref_core(float x, Tab tab /* EXPF_TAB in shared memory */, const ExpConsts &k) {
+  constexpr double SHIFT = 0x1.8p+52;
   const double xd = (double)x;
 #if GSPLAT_EXPF_FMA
-  double kd = __fma_rn(INVLN2N, xd, SHIFT);
+  double kd = __fma_rn(k.invln2n, xd, SHIFT);
   const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
   kd = __dsub_rn(kd, SHIFT);
-  const double r = __fma_rn(INVLN2N, xd, -kd);
+  const double r = __fma_rn(k.invln2n, xd, -kd);
   const double s = __longlong_as_double((long long)(exp_tab_entry(tab, ki & 31ull) + (ki << 47)));
-  const double zz = __fma_rn(C0, r, C1), r2 = __dmul_rn(r, r);
-  double y = __fma_rn(C2, r, 1.0);
+  const double zz = __fma_rn(k.c0, r, k.c1), r2 = __dmul_rn(r, r);
+  double y = __fma_rn(k.c2, r, 1.0);
   y = __fma_rn(zz, r2, y);
   return (float)__dmul_rn(y, s);
 #else
-  const double z = __dmul_rn(INVLN2N, xd);
+  const double z = __dmul_rn(k.invln2n, xd);
   double kd = __dadd_rn(z, SHIFT);
   const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
   kd = __dsub_rn(kd, SHIFT);
   const double r = __dsub_rn(z, kd);
   const double s = __longlong_as_double((long long)(exp_tab_entry(tab, ki & 31ull) + (ki << 47)));
-  const double zz = __dadd_rn(__dmul_rn(C0, r), C1), r2 = __dmul_rn(r, r);
-  double y = __dadd_rn(__dmul_rn(C2, r), 1.0);
+  const double zz = __dadd_rn(__dmul_rn(k.c0, r), k.c1), r2 = __dmul_rn(r, r);
+  double y = __dadd_rn(__dmul_rn(k.c2, r), 1.0);
   y = __dadd_rn(__dmul_rn(zz, r2), y);
   return (float)__dmul_rn(y, s);
 #endif
 }
+template <typename Tab>
+__device__ __forceinline__ float exp_ref_core(float x, Tab tab) { return exp_ref_core(x, tab, exp_consts(false)); }
 __device__ __forceinline__ float exp_ref(float x, const unsigned long long *tab /* EXPF_TAB in shared memory */) {
   if (!(x == x)) return x + x;
   if (x > 88.72283172607421875f) return __int_as_float(0x7f800000);    // 0x1.62e42ep6f: overflow
