@@ -429,3 +429,140 @@ void launch_tile_ranges(const uint32_t *keys, const uint32_t *d_n, uint32_t n_up
 }
 
 }  // namespace gsplat
+
+// ---- K3 without any allocation: gsplat_sort_pairs_static ----------------------------------------
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it).  Same three kernels per digit as launch_radix_sort; everything the sort needs besides the
+// caller's input and output arrays — the ping-pong buffer of the passes in between, the per-tile
+// digit histograms, the digit totals and the element count word — lives in ONE file-scope device
+// array of fixed size.  Every GPU that loads the library holds it (8.5 MiB) until the process exits.
+//
+// The array is shared by every call on a device and keeps the last call's contents: the words that
+// must start at zero are cleared by the call itself, and calls that overlap on the GPU (two streams,
+// two host threads) RACE — serialise them.
+#include "../../include/gsplat_b200.h"
+#include <mutex>
+#include <stdio.h>
+
+namespace gsplat {
+namespace {
+
+constexpr uint32_t STATIC_SORT_MAX = GSPLAT_SORT_STATIC_MAX;                 // elements per call
+static_assert(STATIC_SORT_MAX % RS_TILE == 0, "whole sort tiles");
+constexpr uint32_t STATIC_SORT_TILES = STATIC_SORT_MAX / RS_TILE;            // 512
+// layout of the scratch array, in 32-bit words (every part starts on a 256-byte boundary)
+constexpr size_t SS_KEYS = 0;                                                // [MAX] intermediate keys
+constexpr size_t SS_VALS = SS_KEYS + STATIC_SORT_MAX;                        // [MAX] intermediate values
+constexpr size_t SS_HIST = SS_VALS + STATIC_SORT_MAX;                        // [256 x TILES] per-tile digit counts
+constexpr size_t SS_TOTALS = SS_HIST + (size_t)256 * STATIC_SORT_TILES;      // [256] digit totals
+constexpr size_t SS_COUNT = SS_TOTALS + 256;                                 // [64] word 0 = n
+constexpr size_t SS_WORDS = SS_COUNT + 64;
+
+}  // namespace
+
+// In HOST code this name is a host-side stand-in, not a device address: handing it to a kernel
+// faults (or, where the GPU can reach host memory, silently uses the wrong memory).  The host gets
+// the device address once per device from cudaGetSymbolAddress (static_sort_scratch below).
+static __device__ __align__(256) uint32_t g_static_sort_scratch[SS_WORDS];
+
+// sets the element count and clears the digit totals (the only words of the scratch that are read
+// before they are written when a digit's histogram rows are shorter than the last call's)
+__global__ void static_sort_begin_kernel(uint32_t *scratch, uint32_t n) {
+  const uint32_t t = threadIdx.x;
+  if (t < 256) scratch[SS_TOTALS + t] = 0u;
+  if (t < 64) scratch[SS_COUNT + t] = t == 0 ? n : 0u;
+}
+
+namespace {
+
+// Device address of the scratch array on `device` (which must be current), resolved once per
+// device; also the per-device dynamic-shared-memory opt-in of the sort kernels.
+cudaError_t static_sort_scratch(int device, uint32_t **out) {
+  static std::mutex mu;
+  static uint32_t *addr[256] = {nullptr};
+  if (device < 0 || device >= 256) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[device]) {
+    uint32_t *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void **)&p, g_static_sort_scratch);
+    if (e != cudaSuccess) return e;
+    e = setup_sort_kernels();
+    if (e != cudaSuccess) return e;
+    addr[device] = p;
+  }
+  *out = addr[device];
+  return cudaSuccess;
+}
+
+int static_fail(char *err, size_t err_len, int code, const char *what, const char *detail) {
+  if (err && err_len) snprintf(err, err_len, "gsplat_sort_pairs_static: %s%s%s", what, detail ? ": " : "", detail ? detail : "");
+  return code;
+}
+
+}  // namespace
+}  // namespace gsplat
+
+extern "C" int gsplat_sort_pairs_static(int device, const uint32_t *d_keys_in, const uint32_t *d_values_in,
+                                        uint32_t *d_keys_out, uint32_t *d_values_out, size_t n, int begin_bit,
+                                        int end_bit, void *stream, char *err, size_t err_len) {
+  using namespace gsplat;
+  if (err && err_len) err[0] = 0;
+  if (begin_bit < 0 || end_bit > 32 || begin_bit >= end_bit)
+    return static_fail(err, err_len, GSPLAT_E_ARG, "bit range must satisfy 0 <= begin_bit < end_bit <= 32", nullptr);
+  if (n > STATIC_SORT_MAX) {
+    char msg[96];
+    snprintf(msg, sizeof msg, "n = %zu exceeds the static scratch (GSPLAT_SORT_STATIC_MAX = %u elements)", n,
+             (unsigned)STATIC_SORT_MAX);
+    return static_fail(err, err_len, GSPLAT_E_CAPACITY, msg, nullptr);
+  }
+  if (n == 0) return GSPLAT_OK;
+  if (!d_keys_in || !d_values_in || !d_keys_out || !d_values_out)
+    return static_fail(err, err_len, GSPLAT_E_ARG, "null device pointer", nullptr);
+  if (((uintptr_t)d_keys_in | (uintptr_t)d_values_in | (uintptr_t)d_keys_out | (uintptr_t)d_values_out) & 15u)
+    return static_fail(err, err_len, GSPLAT_E_ARG, "device pointers must be 16-byte aligned", nullptr);
+  if (d_keys_in == d_keys_out || d_values_in == d_values_out)
+    return static_fail(err, err_len, GSPLAT_E_ARG, "input and output arrays must be distinct", nullptr);
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return static_fail(err, err_len, GSPLAT_E_CUDA, "cudaSetDevice", cudaGetErrorString(e));
+  uint32_t *scratch = nullptr;
+  e = static_sort_scratch(device, &scratch);
+  if (e != cudaSuccess) return static_fail(err, err_len, GSPLAT_E_CUDA, "cudaGetSymbolAddress / kernel set-up", cudaGetErrorString(e));
+  cudaStream_t st = (cudaStream_t)stream;
+
+  static_sort_begin_kernel<<<1, 256, 0, st>>>(scratch, (uint32_t)n);
+  ++g_launches;
+  const uint32_t *d_n = scratch + SS_COUNT;
+  int passes, bpp;
+  sort_plan(end_bit - begin_bit, passes, bpp, RS_MAX_BITS);
+  const uint32_t ntiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
+  const uint32_t grid = ntiles < (uint32_t)RS_GRID ? ntiles : (uint32_t)RS_GRID;
+  // pass p reads where pass p - 1 wrote (pass 0: the caller's input) and writes the caller's output
+  // when an even number of passes follows it, the scratch otherwise: the last pass lands in the output
+  const uint32_t *src_k = d_keys_in, *src_v = d_values_in;
+  for (int p = 0; p < passes; ++p) {
+    const bool to_out = ((passes - 1 - p) & 1) == 0;
+    SortBuffers sb{};
+    sb.keys[0] = const_cast<uint32_t *>(src_k); sb.vals[0] = const_cast<uint32_t *>(src_v);
+    sb.keys[1] = to_out ? d_keys_out : scratch + SS_KEYS;
+    sb.vals[1] = to_out ? d_values_out : scratch + SS_VALS;
+    sb.block_hist = scratch + SS_HIST; sb.digit_totals = scratch + SS_TOTALS;
+    sb.capacity = STATIC_SORT_MAX; sb.max_tiles = STATIC_SORT_TILES;
+    const int shift = begin_bit + p * bpp;
+    const int bits = (end_bit - shift) < bpp ? (end_bit - shift) : bpp;
+    g_launches += 3;
+    switch (bits) {
+      case 1: launch_pass<1>(sb, 0, false, d_n, shift, grid, nullptr, st); break;
+      case 2: launch_pass<2>(sb, 0, false, d_n, shift, grid, nullptr, st); break;
+      case 3: launch_pass<3>(sb, 0, false, d_n, shift, grid, nullptr, st); break;
+      case 4: launch_pass<4>(sb, 0, false, d_n, shift, grid, nullptr, st); break;
+      case 5: launch_pass<5>(sb, 0, false, d_n, shift, grid, nullptr, st); break;
+      case 6: launch_pass<6>(sb, 0, false, d_n, shift, grid, nullptr, st); break;
+      default: launch_pass<7>(sb, 0, false, d_n, shift, grid, nullptr, st); break;
+    }
+    src_k = sb.keys[1]; src_v = sb.vals[1];
+  }
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return static_fail(err, err_len, GSPLAT_E_CUDA, "kernel launch", cudaGetErrorString(e));
+  return GSPLAT_OK;
+}

@@ -68,6 +68,8 @@ SYMBOLS = {
     "gsplat_read_tile_lists": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "gsplat_bin_projected": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int]),
     "gsplat_sort_pairs": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, C.c_int]),
+    "gsplat_sort_pairs_static": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, C.c_size_t, C.c_int, C.c_int, _vp,
+                                           C.c_char_p, C.c_size_t]),
     "gsplat_host_alloc": (C.c_int, [C.POINTER(_vp), C.c_size_t]),
     "gsplat_host_free": (C.c_int, [_vp]),
     "gsplat_device_framebuffer": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
@@ -370,6 +372,21 @@ class B200Splatter:
 
     def postprocess_bgr8(self):
         self._check(self.lib.gsplat_postprocess_bgr8(self.h))
+
+
+SORT_STATIC_MAX = 1 << 20   # GSPLAT_SORT_STATIC_MAX (include/gsplat_b200.h)
+
+
+def sort_pairs_static(device: int, d_keys_in: int, d_values_in: int, d_keys_out: int, d_values_out: int, n: int,
+                      begin_bit: int = 0, end_bit: int = 32, stream: int = 0) -> None:
+    """gsplat_sort_pairs_static: the device radix sort on the caller's DEVICE arrays (addresses as
+    ints) with its scratch in a fixed file-scope device array; allocates nothing, asynchronous on
+    `stream`.  Raises GsplatError with the library's message (e.g. n > SORT_STATIC_MAX)."""
+    err = C.create_string_buffer(256)
+    rc = load_library().gsplat_sort_pairs_static(device, d_keys_in, d_values_in, d_keys_out, d_values_out, n,
+                                                 begin_bit, end_bit, stream, err, len(err))
+    if rc != 0:
+        raise GsplatError(rc, err.value.decode())
 
 
 GROUP_VIEWS, GROUP_BANDS = 0, 1

@@ -200,6 +200,21 @@ int gsplat_bin_projected(gsplat_ctx *ctx, const float *depth, const int32_t *rec
  * known-answer tests. */
 int gsplat_sort_pairs(gsplat_ctx *ctx, uint32_t *keys, uint32_t *values, size_t n, int begin_bit,
                       int end_bit);
+/* The same sort without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Needs no gsplat_ctx.  The caller passes DEVICE arrays of
+ * n words each (16-byte aligned, inputs distinct from outputs, on `device`); everything else the sort
+ * needs lives in one file-scope device array of fixed size (8.5 MiB, held by every GPU that loads the
+ * library until the process exits), so n is limited to GSPLAT_SORT_STATIC_MAX elements: a larger n
+ * fails with GSPLAT_E_CAPACITY and a message in `err` (may be NULL).  Stable sort on key bits
+ * [begin_bit, end_bit), asynchronous on `stream` (a cudaStream_t, NULL = default stream); calls no
+ * cudaMalloc / cudaFree.  The array is shared by every call on a device and keeps the last call's
+ * contents (the call clears what it needs cleared): calls that OVERLAP on the GPU race, serialise
+ * them.  The first call on a device resolves the array's address (make it before a capture). */
+#define GSPLAT_SORT_STATIC_MAX (1u << 20)
+int gsplat_sort_pairs_static(int device, const uint32_t *d_keys_in, const uint32_t *d_values_in,
+                             uint32_t *d_keys_out, uint32_t *d_values_out, size_t n, int begin_bit, int end_bit,
+                             void *stream, char *err, size_t err_len);
 
 /* ---- several GPUs of one process ---------------------------------------------
  * The reference drives ONE device (numIpus = 1, numReplicas = 1: src/main/splat.cpp:41-46); its unit
