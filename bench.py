@@ -318,8 +318,9 @@ def stage_rooflines(tm, st, pairs, blended, W, H, tiles, clocks_mhz, peaks):
     mhz = clocks_mhz or peaks.get("sm_max_mhz", 1965.0)
     fp32_peak = 2 * 128 * 148 * mhz * 1e6 / 1e12          # TFLOP/s at the observed SM clock
     alg_bytes = {
-        # scene SoA in, 48 B record per drawn Gaussian + key + rect per Gaussian out; rect re-read by the counts
-        "k1_project": 56 * N + 48 * V + 4 * N + 8 * N + 8 * N,
+        # position + cached 3D covariance (48 B) and colour (16 B) in, 48 B record per drawn Gaussian + key +
+        # rect per Gaussian out; rect re-read by the counts
+        "k1_project": 64 * N + 48 * V + 4 * N + 8 * N + 8 * N,
         # per slice: keys read by the selection (+ rect from the 2nd slice on), selected pairs written;
         # per digit 4 B histogram read + 8 B read + 8 B write per selected Gaussian
         "k3a_sort_depth": 4 * N * S + 8 * N * (S - 1) + 8 * A + 5 * 20 * A,

@@ -87,6 +87,10 @@ struct gsplat_ctx {
   // scene (immutable after upload; the lanes of a dispatcher share lane 0's arrays: scene_owned = false)
   SceneSoA scene{};
   bool scene_owned = true;
+  // scale divisor (bits) the scene's cached ComputeCov3D results were computed for; the lanes of a
+  // dispatcher read lane 0's (cov_state points at the owner's word)
+  uint32_t cov_div_bits = 0xffffffffu;
+  const uint32_t *cov_state = nullptr;
   // per-Gaussian frame buffers
   Projected proj{};
   float *dbg_rec8 = nullptr;
@@ -195,6 +199,10 @@ int fail(gsplat_ctx *c, int code, const std::string &msg) {
   } while (0)
 
 template <typename T> void dfree(T *&p) { if (p) { cudaFree(p); p = nullptr; } }
+void free_scene(SceneSoA &sc) {
+  dfree(sc.pos_c); dfree(sc.cov_a); dfree(sc.cov_b); dfree(sc.rgba); dfree(sc.quat); dfree(sc.scl);
+}
+uint32_t float_bits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
 
 void drop_graphs(gsplat_ctx *ctx) {
   for (auto &g : ctx->graphs) {
@@ -352,7 +360,7 @@ void gsplat_destroy(gsplat_ctx *ctx) {
   cudaSetDevice(ctx->cfg.device);
   if (ctx->st) cudaStreamSynchronize(ctx->st);
   drop_graphs(ctx);
-  if (ctx->scene_owned) { dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12); }
+  if (ctx->scene_owned) free_scene(ctx->scene);
   dfree(ctx->proj.rec); dfree(ctx->proj.rect);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4); dfree(ctx->frame_block); dfree(ctx->d_persist); dfree(ctx->chain_block);
   dfree(ctx->proj.depth_key);
@@ -531,33 +539,55 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
   return GSPLAT_OK;
 }
 
+// The scene's cached ComputeCov3D results (SceneSoA) belong to ONE scale divisor.  Called when the
+// scene or the camera parameters of the context that OWNS the arrays change: recomputes them if the
+// divisor differs, synchronously (rare: an upload, or the UI's scale slider).  Lanes that share the
+// arrays are drained by the dispatcher before it routes the new camera (gsplat_set_camera).
+static int refresh_cov3(gsplat_ctx *ctx) {
+  if (!ctx->scene_owned || !ctx->have_scene || !ctx->have_camera) return GSPLAT_OK;
+  const uint32_t want = float_bits(ctx->fp.scale_div);
+  if (ctx->cov_div_bits == want) return GSPLAT_OK;
+  CU(cudaSetDevice(ctx->cfg.device));
+  CU(cudaStreamSynchronize(ctx->st));
+  launch_cov3(ctx->scene, ctx->fp.scale_div, ctx->st);
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(ctx->st));
+  ctx->cov_div_bits = want;
+  return GSPLAT_OK;
+}
+
 // Scene upload of one (lane) context.  `shared` != nullptr: adopt another lane's device arrays
 // instead of uploading a copy (the scene is read-only after upload; only the per-frame working
 // buffers are per lane).
-static int upload_scene_impl(gsplat_ctx *ctx, const float *g16, size_t n, const SceneSoA *shared) {
+static int upload_scene_impl(gsplat_ctx *ctx, const float *g16, size_t n, gsplat_ctx *shared) {
   if (!ctx || (!g16 && n && !shared)) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: null argument");
   if (n > 0x7fffffffull) return fail(ctx, GSPLAT_E_ARG, "gsplat_upload_scene: too many Gaussians");
   CU(cudaSetDevice(ctx->cfg.device));
   CU(cudaStreamSynchronize(ctx->st));
   drop_graphs(ctx);
   for (auto &sl : ctx->slots) sl.pending = false;
-  if (ctx->scene_owned) { dfree(ctx->scene.pos_s0); dfree(ctx->scene.quat); dfree(ctx->scene.rgba); dfree(ctx->scene.s12); }
+  if (ctx->scene_owned) free_scene(ctx->scene);
   ctx->scene = SceneSoA{};
   ctx->scene_owned = true;
+  ctx->cov_div_bits = 0xffffffffu;
+  ctx->cov_state = &ctx->cov_div_bits;
   dfree(ctx->proj.rec); dfree(ctx->proj.rect); dfree(ctx->chain_block);
   dfree(ctx->proj.depth_key);
   dfree(ctx->dbg_rec8); dfree(ctx->dbg_rect4);
   ctx->have_scene = ctx->have_frame = false;
   const size_t na = n ? n : 1;
   if (shared) {
-    ctx->scene = *shared;
+    ctx->scene = shared->scene;
     ctx->scene_owned = false;
+    ctx->cov_state = &shared->cov_div_bits;
   } else {
     ctx->scene.n = (uint32_t)n;
-    CU(cudaMalloc(&ctx->scene.pos_s0, na * sizeof(float4)));
-    CU(cudaMalloc(&ctx->scene.quat, na * sizeof(float4)));
+    CU(cudaMalloc(&ctx->scene.pos_c, na * sizeof(float4)));
+    CU(cudaMalloc(&ctx->scene.cov_a, na * sizeof(float4)));
+    CU(cudaMalloc(&ctx->scene.cov_b, na * sizeof(float4)));
     CU(cudaMalloc(&ctx->scene.rgba, na * sizeof(float4)));
-    CU(cudaMalloc(&ctx->scene.s12, na * sizeof(float2)));
+    CU(cudaMalloc(&ctx->scene.quat, na * sizeof(float4)));
+    CU(cudaMalloc(&ctx->scene.scl, na * sizeof(float4)));
   }
   CU(cudaMalloc(&ctx->proj.rec, na * 3 * sizeof(float4)));
   CU(cudaMemsetAsync(ctx->proj.rec, 0, na * 3 * sizeof(float4), ctx->st));
@@ -598,7 +628,7 @@ static int upload_scene_impl(gsplat_ctx *ctx, const float *g16, size_t n, const 
     if (rc) return rc;
   }
   ctx->have_scene = true;
-  return GSPLAT_OK;
+  return refresh_cov3(ctx);
 }
 
 int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
@@ -608,12 +638,12 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
       gsplat_ctx *lane = ctx->lanes[l];
       cudaSetDevice(lane->cfg.device);
       cudaStreamSynchronize(lane->st);
-      if (!lane->scene_owned) { lane->scene = SceneSoA{}; lane->scene_owned = true; lane->have_scene = false; }
+      if (!lane->scene_owned) { lane->scene = SceneSoA{}; lane->scene_owned = true; lane->have_scene = false; lane->cov_state = &lane->cov_div_bits; }
     }
     int rc = upload_scene_impl(first, g16, n, nullptr);
     if (rc < 0) { ctx->err = first->err; return rc; }
     for (size_t l = 1; l < ctx->lanes.size(); ++l) {
-      rc = upload_scene_impl(ctx->lanes[l], nullptr, n, &first->scene);
+      rc = upload_scene_impl(ctx->lanes[l], nullptr, n, first);
       if (rc < 0) { ctx->err = ctx->lanes[l]->err; return rc; }
     }
     return GSPLAT_OK;
@@ -622,6 +652,10 @@ int gsplat_upload_scene(gsplat_ctx *ctx, const float *g16, size_t n) {
 }
 
 int gsplat_set_camera(gsplat_ctx *ctx, const float mv[16], const float proj[16], float fov, float scale_div) {
+  if (ctx && !ctx->lanes.empty() && ctx->lanes[0]->cov_div_bits != float_bits(scale_div)) {
+    // the lanes share lane 0's covariance cache, which is about to be recomputed: drain them all
+    for (gsplat_ctx *lane : ctx->lanes) { cudaSetDevice(lane->cfg.device); cudaStreamSynchronize(lane->st); }
+  }
   ROUTE_ALL(gsplat_set_camera(ctx, mv, proj, fov, scale_div));
   if (!ctx || !mv || !proj) return fail(ctx, GSPLAT_E_ARG, "gsplat_set_camera: null argument");
   FrameParams &fp = ctx->fp;
@@ -641,7 +675,7 @@ int gsplat_set_camera(gsplat_ctx *ctx, const float mv[16], const float proj[16],
   fp.tiles_across = ctx->tiles_across; fp.tiles_down = ctx->tiles_down;
   fp.row_begin = ctx->cfg.band_row_begin; fp.row_end = ctx->cfg.band_row_end;
   ctx->have_camera = true;
-  return GSPLAT_OK;
+  return refresh_cov3(ctx);
 }
 
 int gsplat_set_band(gsplat_ctx *ctx, int row_begin, int row_end) {

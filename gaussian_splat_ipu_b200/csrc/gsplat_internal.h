@@ -21,13 +21,21 @@ struct FrameParams {
   int row_begin, row_end;   // tile-row band rendered by this context
 };
 
-// Scene in HBM: exactly the 56 live bytes of the reference's 256-byte-strided record
-// (SURVEY §8 a1).  w == 1 and gid == index+1 are implicit; empty slots have a NaN position.
+// Scene in HBM: the 56 live bytes of the reference's 256-byte-strided record plus
+// the camera-independent part of the projection, cached.  w == 1 and gid == index+1 are implicit;
+// empty slots have a NaN position.
+// Gaussian3D::ComputeCov3D (ipu_geometry.hpp:315-323) depends on the Gaussian and on fxy[1] (the
+// scale divisor) only, not on the camera: its nine f32 results are computed once per (scene,
+// divisor) by cov3_kernel — same operations, same order, so the same bits as the reference's
+// per-frame evaluation — and K1 reads them (36 B) instead of quaternion + log-scales (28 B) and
+// the three expf, the normalisation and two 3x3 products per Gaussian per frame.
 struct SceneSoA {
-  float4 *pos_s0;    // x, y, z, log-scale.x
-  float4 *quat;      // w, x, y, z   (rot_0 = w, ipu_geometry.hpp:317)
-  float4 *rgba;      // r, g, b, opacity (raw)
-  float2 *s12;       // log-scale.y, log-scale.z
+  float4 *pos_c;     // x, y, z, cov3[2][2]                      (K1 input)
+  float4 *cov_a;     // cov3[0][0], [0][1], [0][2], [1][0]       (K1 input; glm [col][row])
+  float4 *cov_b;     // cov3[1][1], [1][2], [2][0], [2][1]       (K1 input)
+  float4 *rgba;      // r, g, b, opacity (raw)                    (K1 input, drawn Gaussians)
+  float4 *quat;      // w, x, y, z   (rot_0 = w, ipu_geometry.hpp:317)   (cov3_kernel input)
+  float4 *scl;       // log-scale.x, .y, .z, unused                     (cov3_kernel input)
   uint32_t n;
 };
 
@@ -209,6 +217,8 @@ constexpr int BAND_WORD_OFFSET = 2;
 
 // ---- launchers (all asynchronous on `st`) ------------------------------------------------
 void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st);
+// the cached ComputeCov3D results of every Gaussian for scale divisor fxy[1] = scale_div
+void launch_cov3(const SceneSoA &scene, float scale_div, cudaStream_t st);
 // K1: writes Projected; drawn_counter += number of drawn Gaussians (V).
 void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *drawn_counter,
                     float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st);

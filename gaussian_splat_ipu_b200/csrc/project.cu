@@ -5,8 +5,8 @@
 // separately rounded IEEE f32 operation in the order glm 0.9.9.9 evaluates it on the host
 // (the reference's codelet is plain glm arithmetic, include/splat/ipu_geometry.hpp:315-383), so
 // K1 is bit-identical to the host-compiled reference, exp() included (glibc's expf algorithm is
-// restated below).  K1 is HBM-bound (56 B in,
-// 52 B out per Gaussian), so the unfused arithmetic costs nothing measurable.
+// restated in gsplat_internal.h).  The camera-independent part (ComputeCov3D) is cached per scene and
+// scale divisor (cov3_kernel); K1 itself reads 64 B and writes 60 B per drawn Gaussian.
 #include "gsplat_internal.h"
 
 namespace gsplat {
@@ -72,23 +72,17 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
     drawn_counter[BAND_WORD_OFFSET + 1] = (uint32_t)fp.row_end;
   }
   __shared__ uint32_t red[K1_THREADS / 32];
-  // the exp table is indexed per thread: from constant memory every distinct index of a warp is a
-  // separate replay, from shared memory it is one (at worst two-way conflicted) access
-  __shared__ unsigned long long exp_tab[32];
-  if (threadIdx.x < 32) exp_tab[threadIdx.x] = EXPF_TAB[threadIdx.x];
-  __syncthreads();
   const uint32_t i = blockIdx.x * K1_THREADS + threadIdx.x;
   uint32_t touched = 0;
   if (i < s.n) {
-    const float4 p = __ldg(&s.pos_s0[i]);
+    const float4 p = __ldg(&s.pos_c[i]);
     const bool live = (p.x == p.x);   // empty slots (gid <= 0, codelets.cpp:456) carry a NaN position
     int c0 = 0, c1 = -1, r0 = 0, r1 = -1;
     uint2 rect_out = make_uint2(RECT_EMPTY, RECT_EMPTY);
     float px = 0.f, py = 0.f, cz = 0.f, cova = 0.f, covb = 0.f, covc = 0.f, rad = 0.f;
     bool drawn = false;
     if (live) {
-      const float2 s12 = __ldg(&s.s12[i]);
-      const float4 q = __ldg(&s.quat[i]);
+      const float4 ca = __ldg(&s.cov_a[i]), cb = __ldg(&s.cov_b[i]);
       const float *m = fp.mvp;
       // clip = mvp * (x,y,z,1): glm type_mat4x4.inl:561-572, (m0*v0 + m1*v1) + (m2*v2 + m3*v3)
       float clip[4];
@@ -102,30 +96,12 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
       px *= fp.img_w; py *= fp.img_h;
       px += 0.0f; py += 0.0f;
       cz = clip[2];
-      // g.scale = g.scale / fxy[1], codelets.cpp:463
-      // g.scale / fxy[1] (codelets.cpp:463); x / 1.0f is x exactly, and an IEEE division is ~12
-      // instructions: skip the three of them for the true-scale divisor (uniform branch)
-      float sc0 = p.w, sc1 = s12.x, sc2 = s12.y;
-      if (fp.scale_div != 1.0f) { sc0 = sc0 / fp.scale_div; sc1 = sc1 / fp.scale_div; sc2 = sc2 / fp.scale_div; }
-
-      // ---- Gaussian3D::ComputeCov3D, ipu_geometry.hpp:315-323 (glm normalize + mat3_cast)
-      float w = q.x, x = q.y, y = q.z, z = q.w;
-      const float len = sqrtf((w * w + x * x) + (y * y + z * z));
-      if (len <= 0.0f) { w = 1.f; x = 0.f; y = 0.f; z = 0.f; }
-      else { const float inv = 1.0f / len; w = w * inv; x = x * inv; y = y * inv; z = z * inv; }
-      const float qxx = x * x, qyy = y * y, qzz = z * z, qxz = x * z, qxy = x * y, qyz = y * z;
-      const float qwx = w * x, qwy = w * y, qwz = w * z;
-      M3 R;
-      R.c[0][0] = 1.f - 2.f * (qyy + qzz); R.c[0][1] = 2.f * (qxy + qwz); R.c[0][2] = 2.f * (qxz - qwy);
-      R.c[1][0] = 2.f * (qxy - qwz); R.c[1][1] = 1.f - 2.f * (qxx + qzz); R.c[1][2] = 2.f * (qyz + qwx);
-      R.c[2][0] = 2.f * (qxz + qwy); R.c[2][1] = 2.f * (qyz - qwx); R.c[2][2] = 1.f - 2.f * (qxx + qyy);
-      M3 S;
-#pragma unroll
-      for (int c = 0; c < 3; ++c)
-#pragma unroll
-        for (int k = 0; k < 3; ++k) S.c[c][k] = 0.f;
-      S.c[0][0] = exp_ref(sc0, exp_tab); S.c[1][1] = exp_ref(sc1, exp_tab); S.c[2][2] = exp_ref(sc2, exp_tab);
-      const M3 cov3 = m3_mul(m3_mul(m3_mul(R, S), m3_t(S)), m3_t(R));
+      // ---- Gaussian3D::ComputeCov3D (ipu_geometry.hpp:315-323): camera independent, cached by
+      // cov3_kernel below for the frame's scale divisor
+      M3 cov3;
+      cov3.c[0][0] = ca.x; cov3.c[0][1] = ca.y; cov3.c[0][2] = ca.z;
+      cov3.c[1][0] = ca.w; cov3.c[1][1] = cb.x; cov3.c[1][2] = cb.y;
+      cov3.c[2][0] = cb.z; cov3.c[2][1] = cb.w; cov3.c[2][2] = p.w;
 
       // ---- Gaussian3D::ComputeCov2D, ipu_geometry.hpp:333-383.  mv is the FULL projection*view
       // product and tan_fovy == tan_fovx (reference quirks, kept): t == clip.
@@ -260,17 +236,64 @@ inject_kernel(const float *__restrict__ depth, const int32_t *__restrict__ rect4
   if (threadIdx.x == 0 && nd) atomicAdd(drawn_counter, nd);
 }
 
-// Scene upload: reference AoS records (16 floats) -> SoA (56 live bytes).
+// Scene upload: reference AoS records (16 floats) -> SoA (56 live bytes; the covariance cache is
+// filled by cov3_kernel).
 __global__ void aos_to_soa_kernel(const float4 *__restrict__ aos, SceneSoA s) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= s.n) return;
   const float4 mean = aos[(size_t)i * 4 + 0], col = aos[(size_t)i * 4 + 1];
   const float4 rot = aos[(size_t)i * 4 + 2], sg = aos[(size_t)i * 4 + 3];
   const bool live = sg.w > 0.f;   // gid > 0
-  s.pos_s0[i] = make_float4(live ? mean.x : __int_as_float(0x7fc00000), mean.y, mean.z, sg.x);
+  s.pos_c[i] = make_float4(live ? mean.x : __int_as_float(0x7fc00000), mean.y, mean.z, 0.f);
   s.quat[i] = rot;
   s.rgba[i] = col;
-  s.s12[i] = make_float2(sg.y, sg.z);
+  s.scl[i] = make_float4(sg.x, sg.y, sg.z, 0.f);
+}
+
+// Gaussian3D::ComputeCov3D for every Gaussian (ipu_geometry.hpp:315-323, after codelets.cpp:463's
+// g.scale / fxy[1]): cov3 = R S S^T R^T in glm's evaluation order, exp() as the host libm's.  Runs
+// when the scene or the scale divisor changes, not per frame.
+__global__ void __launch_bounds__(K1_THREADS)
+cov3_kernel(SceneSoA s, float scale_div) {
+  // the exp table is indexed per thread: from constant memory every distinct index of a warp is a
+  // separate replay, from shared memory it is one (at worst two-way conflicted) access
+  __shared__ unsigned long long exp_tab[32];
+  if (threadIdx.x < 32) exp_tab[threadIdx.x] = EXPF_TAB[threadIdx.x];
+  __syncthreads();
+  const uint32_t i = blockIdx.x * K1_THREADS + threadIdx.x;
+  if (i >= s.n) return;
+  const float4 sl = s.scl[i];
+  const float4 q = s.quat[i];
+  // g.scale / fxy[1] (codelets.cpp:463); x / 1.0f is x exactly
+  float sc0 = sl.x, sc1 = sl.y, sc2 = sl.z;
+  if (scale_div != 1.0f) { sc0 = sc0 / scale_div; sc1 = sc1 / scale_div; sc2 = sc2 / scale_div; }
+  // glm normalize + mat3_cast
+  float w = q.x, x = q.y, y = q.z, z = q.w;
+  const float len = sqrtf((w * w + x * x) + (y * y + z * z));
+  if (len <= 0.0f) { w = 1.f; x = 0.f; y = 0.f; z = 0.f; }
+  else { const float inv = 1.0f / len; w = w * inv; x = x * inv; y = y * inv; z = z * inv; }
+  const float qxx = x * x, qyy = y * y, qzz = z * z, qxz = x * z, qxy = x * y, qyz = y * z;
+  const float qwx = w * x, qwy = w * y, qwz = w * z;
+  M3 R;
+  R.c[0][0] = 1.f - 2.f * (qyy + qzz); R.c[0][1] = 2.f * (qxy + qwz); R.c[0][2] = 2.f * (qxz - qwy);
+  R.c[1][0] = 2.f * (qxy - qwz); R.c[1][1] = 1.f - 2.f * (qxx + qzz); R.c[1][2] = 2.f * (qyz + qwx);
+  R.c[2][0] = 2.f * (qxz + qwy); R.c[2][1] = 2.f * (qyz - qwx); R.c[2][2] = 1.f - 2.f * (qxx + qyy);
+  M3 S;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) S.c[c][k] = 0.f;
+  S.c[0][0] = exp_ref(sc0, exp_tab); S.c[1][1] = exp_ref(sc1, exp_tab); S.c[2][2] = exp_ref(sc2, exp_tab);
+  const M3 cov3 = m3_mul(m3_mul(m3_mul(R, S), m3_t(S)), m3_t(R));
+  s.cov_a[i] = make_float4(cov3.c[0][0], cov3.c[0][1], cov3.c[0][2], cov3.c[1][0]);
+  s.cov_b[i] = make_float4(cov3.c[1][1], cov3.c[1][2], cov3.c[2][0], cov3.c[2][1]);
+  s.pos_c[i].w = cov3.c[2][2];
+}
+
+void launch_cov3(const SceneSoA &scene, float scale_div, cudaStream_t st) {
+  if (!scene.n) return;
+  ++g_launches;
+  cov3_kernel<<<ceil_div(scene.n, K1_THREADS), K1_THREADS, 0, st>>>(scene, scale_div);
 }
 
 void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st) {
