@@ -35,6 +35,7 @@
 // whose block few splats reach runs ahead of its neighbours by up to the ring depth.
 // FP32-pipe bound; no tensor cores (each pair has its own quadratic form).
 #include "gsplat_internal.h"
+#include <stdlib.h>
 
 namespace gsplat {
 
@@ -48,7 +49,11 @@ constexpr float ALPHA_MIN = 1.0f / 255.0f;
 #ifndef GSPLAT_BLEND_BATCH
 #define GSPLAT_BLEND_BATCH 128
 #endif
+#ifndef GSPLAT_BLEND_AHEAD
+#define GSPLAT_BLEND_AHEAD 2
+#endif
 constexpr int BLEND_STAGES = GSPLAT_BLEND_STAGES;    // ring depth
+constexpr uint32_t BLEND_AHEAD = GSPLAT_BLEND_AHEAD; // stages between an entry's index load and its record copy
 constexpr int BLEND_BATCH = GSPLAT_BLEND_BATCH;      // list entries per ring stage (multiple of 32)
 static_assert(BLEND_BATCH % 32 == 0, "consumers walk a stage in chunks of 32 entries");
 constexpr int BLEND_MAX_WARPS = 20;                  // consumer warps of an undivided 32 x 20 tile
@@ -71,6 +76,10 @@ constexpr int BLEND_MAX_WARPS = 20;                  // consumer warps of an und
 #ifndef GSPLAT_BLEND_HITLIST
 #define GSPLAT_BLEND_HITLIST 0
 #endif
+// 1 = a consumer warp tests all of a stage's entries against its block before it walks any (0 = chunk by chunk)
+#ifndef GSPLAT_BLEND_STAGETEST
+#define GSPLAT_BLEND_STAGETEST 1
+#endif
 // 1 = phase B's turn is straight-line (selects), 0 = branches per test (measured: 0.331 against 0.361 ms)
 #ifndef GSPLAT_BLEND_PRED
 #define GSPLAT_BLEND_PRED 1
@@ -86,7 +95,9 @@ struct BlendSmem {
   unsigned long long full[BLEND_STAGES];             // mbarrier: the stage's bytes have landed
   unsigned long long empty[BLEND_STAGES];            // mbarrier: every consumer warp is done with the stage
   unsigned long long exp_tab[32];                    // exp_ref's 2^(k/32) table
+#if GSPLAT_BLEND_HITLIST
   uint32_t hits[BLEND_MAX_WARPS][34];                // per consumer warp: lanes of the chunk's hit entries, in order
+#endif
   uint32_t warps_done;                               // consumer warps whose 32 pixels have all stopped
   uint32_t strip_done[4];                            // the same per 8-pixel column strip of the part
   uint32_t stop;                                     // producer: nothing more will be staged
@@ -286,15 +297,19 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
 
   if (warp == NW) {
     // ---- producer: the tile's list, BLEND_BATCH entries per stage --------------------------------
-    // The list indices of stage it + 1 are loaded while the producer waits for stage it's slot, so a
-    // stage costs the producer one round trip (the record copies, asynchronous), not two.
+    // The list indices are loaded BLEND_AHEAD stages before their records are copied: with the ring
+    // not full (consumers that reject nearly everything: the long lists of the later slices), a stage
+    // costs the producer 1 / BLEND_AHEAD of an index round trip instead of a whole one, and the record
+    // copies of up to BLEND_STAGES stages are in flight behind it.
     constexpr uint32_t PER_LANE = BLEND_BATCH / 32;
-    uint32_t gidx[PER_LANE];
+    uint32_t gidx[BLEND_AHEAD][PER_LANE];
 #pragma unroll
-    for (uint32_t q = 0; q < PER_LANE; ++q) {
-      const uint32_t j = q * 32 + lane;
-      gidx[q] = j < n ? __ldg(&vals[range.x + j]) : 0u;
-    }
+    for (uint32_t a = 0; a < BLEND_AHEAD; ++a)
+#pragma unroll
+      for (uint32_t q = 0; q < PER_LANE; ++q) {
+        const uint32_t j = a * BLEND_BATCH + q * 32 + lane;
+        gidx[a][q] = j < n ? __ldg(&vals[range.x + j]) : 0u;
+      }
     for (uint32_t it = 0; it < nbatch; ++it) {
       const uint32_t stage = it % BLEND_STAGES, use = it / BLEND_STAGES;
       mbar_wait(&sm.empty[stage], (use & 1u) ^ 1u);        // first use of a stage: passes at once
@@ -313,7 +328,7 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       for (uint32_t q = 0; q < PER_LANE; ++q) {
         const uint32_t j = q * 32 + lane;
         if (j < cnt) {
-          const float4 *src = p.rec + (size_t)gidx[q] * 3;
+          const float4 *src = p.rec + (size_t)gidx[0][q] * 3;
           float4 *dst = &sm.ring[stage][j * 3];
 #if GSPLAT_BLEND_TMA
           bulk_copy_48(dst, src, &sm.full[stage]);
@@ -326,9 +341,11 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       async_copies_arrive(&sm.full[stage]);   // every lane: one of the 32 arrivals, once its copies have landed
 #endif
 #pragma unroll
-      for (uint32_t q = 0; q < PER_LANE; ++q) {            // next stage's indices
-        const uint32_t j = base + BLEND_BATCH + q * 32 + lane;
-        gidx[q] = j < n ? __ldg(&vals[range.x + j]) : 0u;
+      for (uint32_t q = 0; q < PER_LANE; ++q) {            // indices of stage it + BLEND_AHEAD
+#pragma unroll
+        for (uint32_t a = 0; a + 1 < BLEND_AHEAD; ++a) gidx[a][q] = gidx[a + 1][q];
+        const uint32_t j = base + BLEND_AHEAD * BLEND_BATCH + q * 32 + lane;
+        gidx[BLEND_AHEAD - 1][q] = j < n ? __ldg(&vals[range.x + j]) : 0u;
       }
     }
   } else {
@@ -374,8 +391,33 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       if (!warp_done) {
         const uint32_t base = it * BLEND_BATCH, cnt = min((uint32_t)BLEND_BATCH, n - base);
         const float4 *ring = sm.ring[stage];
-        for (uint32_t c0 = 0; c0 < cnt; c0 += 32) {
-          // lane = entry: does the box around its alpha >= 1/255 ellipse reach this warp's block?
+        // lane = entry: does the box around its alpha >= 1/255 ellipse reach this warp's block?
+        // The WHOLE stage is tested first (BLEND_BATCH / 32 independent loads and ballots per lane): a
+        // warp's instructions issue ~16 cycles apart, so testing the chunks one after the other made
+        // a stage without a single hit cost four dependent test sequences — and the long, mostly
+        // irrelevant lists of the later slices are walked at exactly that latency (they were the
+        // critical path of those launches: SMs active 70 % of the launch, profiles/).
+        constexpr uint32_t CHUNKS = BLEND_BATCH / 32;
+        uint32_t masks[CHUNKS];
+#if GSPLAT_BLEND_STAGETEST
+#pragma unroll
+        for (uint32_t h = 0; h < CHUNKS; ++h) {
+          const uint32_t jj = h * 32 + lane;
+          bool hit = false;
+          if (jj < cnt) {
+            const float4 a = ring[jj * 3];
+            hit = fabsf(a.x - bcx) <= a.z + 3.5f && fabsf(a.y - bcy) <= a.w + 1.5f;
+          }
+          masks[h] = __ballot_sync(0xffffffffu, hit);
+        }
+#endif
+#pragma unroll
+        for (uint32_t h = 0; h < CHUNKS; ++h) {
+          const uint32_t c0 = h * 32;
+#if GSPLAT_BLEND_STAGETEST
+          uint32_t mask = masks[h];
+#else
+          if (c0 >= cnt) break;
           const uint32_t jj = c0 + lane;
           bool hit = false;
           if (jj < cnt) {
@@ -383,6 +425,8 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
             hit = fabsf(a.x - bcx) <= a.z + 3.5f && fabsf(a.y - bcy) <= a.w + 1.5f;
           }
           uint32_t mask = __ballot_sync(0xffffffffu, hit);
+#endif
+          if (mask == 0) continue;
           // Phase A, whole warp per entry: the fused pre-test q = A dx^2 + 2 B dx dy + C dy^2 against
           // qmax (alpha < 1/255 beyond it) gives every pixel the set of chunk entries it must blend.
           // Two entries per turn (their loads and pre-tests overlap).
@@ -547,6 +591,13 @@ static void launch_tile_order(const uint2 *ranges, const FrameParams &fp, const 
   tile_order_kernel<<<1, 1024, 0, st>>>(ranges, fp.tiles_across, band, first ? nullptr : tile_done, order);
 }
 
+// Dynamic shared memory per K5 CTA.  GSPLAT_K5_SMEM_PAD (bytes, experiments) pads it to lower the number
+// of K5 CTAs resident per SM, which leaves room for another lane's K1 / sort CTAs beside them.
+static size_t blend_smem_bytes() {
+  static const size_t pad = [] { const char *e = getenv("GSPLAT_K5_SMEM_PAD"); return e ? (size_t)atol(e) : (size_t)0; }();
+  return sizeof(BlendSmem) + pad;
+}
+
 template <bool COUNT, bool FIRST, bool LAST>
 static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
                            const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split,
@@ -557,13 +608,13 @@ static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, cons
   const int part_w = 32 >> split_log2;                            // columns per CTA
   const int warps = (part_w / 8) * ((full_h + 3) / 4);           // one consumer warp per 8 x 4 pixel block
   ++g_launches;
-  blend_kernel<COUNT, FIRST, LAST><<<(rows * fp.tiles_across) << split_log2, (warps + 1) * 32, sizeof(BlendSmem), st>>>(
+  blend_kernel<COUNT, FIRST, LAST><<<(rows * fp.tiles_across) << split_log2, (warps + 1) * 32, blend_smem_bytes(), st>>>(
       p, sorted_vals, ranges, fp.tiles_across, band, full_h, split_log2, fb_tiled, tstate, ts, order, pair_counters);
 }
 
 template <bool COUNT, bool FIRST, bool LAST> static cudaError_t blend_attr() {
   return cudaFuncSetAttribute(blend_kernel<COUNT, FIRST, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)sizeof(BlendSmem));
+                              (int)blend_smem_bytes());
 }
 // Dynamic shared memory opt-in of every K5 variant on the CURRENT device (the attribute belongs to
 // the device's context: gsplat_create runs this once per device).
