@@ -87,6 +87,7 @@ struct gsplat_ctx {
   // scene (immutable after upload; the lanes of a dispatcher share lane 0's arrays: scene_owned = false)
   SceneSoA scene{};
   bool scene_owned = true;
+  bool is_lane = false;      // one of a dispatcher's lanes (several frames in flight)
   // scale divisor (bits) the scene's cached ComputeCov3D results were computed for; the lanes of a
   // dispatcher read lane 0's (cov_state points at the owner's word)
   uint32_t cov_div_bits = 0xffffffffu;
@@ -214,6 +215,7 @@ void drop_graphs(gsplat_ctx *ctx) {
 
 void free_sort(SortBuffers &s) {
   dfree(s.keys[0]); dfree(s.keys[1]); dfree(s.vals[0]); dfree(s.vals[1]); dfree(s.block_hist); dfree(s.digit_totals);
+  dfree(s.tile_state); dfree(s.sweep_ctl);
   s.capacity = 0; s.max_tiles = 0;
 }
 
@@ -232,6 +234,19 @@ int alloc_sort(gsplat_ctx *ctx, SortBuffers &s, size_t capacity) {
   CU(cudaMalloc(&s.block_hist, (size_t)256 * s.max_tiles * sizeof(uint32_t)));
   CU(cudaMalloc(&s.digit_totals, 256 * sizeof(uint32_t)));
   CU(cudaMemset(s.digit_totals, 0, 256 * sizeof(uint32_t)));
+  // Which form of the sort passes (radix_sort.cu).  Measured on the 6 M bench frame (profiles/ab_sort_r2.txt):
+  // the single-sweep passes take 50 us off a frame's latency (57 -> 33 launches) but their waiting
+  // CTAs cost a context with several frames in flight 1 % of its throughput, so a context that
+  // renders one frame at a time gets them and the lanes of a dispatcher keep the three-kernel passes.
+  // GSPLAT_SORT_SWEEP=0/1 forces one or the other.
+  bool sweep = !ctx->is_lane;
+  if (const char *e = std::getenv("GSPLAT_SORT_SWEEP")) sweep = std::atoi(e) != 0;
+  if (sweep) {
+    CU(cudaMalloc(&s.tile_state, (size_t)256 * s.max_tiles * sizeof(unsigned long long)));
+    CU(cudaMemset(s.tile_state, 0, (size_t)256 * s.max_tiles * sizeof(unsigned long long)));
+    CU(cudaMalloc(&s.sweep_ctl, RS_SWEEP_CTL_WORDS * sizeof(uint32_t)));
+    CU(cudaMemset(s.sweep_ctl, 0, RS_SWEEP_CTL_WORDS * sizeof(uint32_t)));
+  }
   s.capacity = (uint32_t)capacity;
   return GSPLAT_OK;
 }
@@ -441,6 +456,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
           delete outer;
           return rc;
         }
+        lane->is_lane = true;
         outer->lanes.push_back(lane);
       }
       cudaSetDevice(cfg->device);
@@ -672,6 +688,20 @@ int gsplat_set_camera(gsplat_ctx *ctx, const float mv[16], const float proj[16],
   fp.tile_w = (float)ctx->cfg.tile_w; fp.tile_h = (float)ctx->cfg.tile_h;
   // tb.diagonal().length() * clipSize (codelets.cpp:470,622; ipu_geometry.hpp:53-55,116-118)
   fp.guard = std::sqrt(fp.tile_w * fp.tile_w + fp.tile_h * fp.tile_h) * ctx->cfg.guard_factor;
+  {
+    // K1 tests the squared diagonal against guard_sq instead of taking a square root per Gaussian.
+    // sqrtf is correctly rounded and monotone, so the set {q : sqrtf(q) >= guard} is an upper set of
+    // the floats; its least element is found by stepping from guard * guard.
+    float q = fp.guard * fp.guard;
+    if (fp.guard > 0.f && std::isfinite(q)) {
+      while (q > 0.f && std::sqrt(std::nextafter(q, 0.f)) >= fp.guard) q = std::nextafter(q, 0.f);
+      while (std::isfinite(q) && std::sqrt(q) < fp.guard) q = std::nextafter(q, INFINITY);
+    }
+    if (!(fp.guard > 0.f)) q = 0.f;      // sqrtf(x) < guard never holds
+    fp.guard_sq = q;
+    int e = 0;
+    fp.inv_tile_w = std::frexp(fp.tile_w, &e) == 0.5f ? 1.0f / fp.tile_w : 0.0f;
+  }
   fp.tiles_across = ctx->tiles_across; fp.tiles_down = ctx->tiles_down;
   fp.row_begin = ctx->cfg.band_row_begin; fp.row_end = ctx->cfg.band_row_end;
   ctx->have_camera = true;

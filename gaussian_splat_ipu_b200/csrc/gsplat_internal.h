@@ -17,6 +17,8 @@ struct FrameParams {
   float img_w, img_h;
   float tile_w, tile_h;
   float guard;       // |tile diagonal| * clipSize
+  float guard_sq;    // smallest float q with sqrtf(q) >= guard: sqrtf(x) < guard  <=>  x < guard_sq (exactly)
+  float inv_tile_w;  // 1 / tile_w when tile_w is a power of two (x / tile_w == x * inv_tile_w exactly), else 0
   int tiles_across, tiles_down;
   int row_begin, row_end;   // tile-row band rendered by this context
 };
@@ -237,7 +239,19 @@ struct SortBuffers {
   uint32_t *digit_totals;   // 256
   uint32_t capacity;        // elements
   uint32_t max_tiles;
+  // single-sweep passes (launch_radix_sort, RS_SWEEP): per (tile, digit) look-back words and the
+  // self-cleaning control block (RsSweepCtl); nullptr selects the three-kernel passes
+  unsigned long long *tile_state;   // 256 * max_tiles
+  uint32_t *sweep_ctl;              // RS_SWEEP_CTL_WORDS, zero at rest
 };
+// sweep_ctl layout (words): digit totals of every pass [RS_SWEEP_MAX_PASSES][256], then per pass a
+// tile ticket and an exit counter, then the sort serial number
+constexpr int RS_SWEEP_MAX_PASSES = 8;
+constexpr int RS_SWEEP_HIST = 0;
+constexpr int RS_SWEEP_TICKET = RS_SWEEP_MAX_PASSES * 256;
+constexpr int RS_SWEEP_EXIT = RS_SWEEP_TICKET + RS_SWEEP_MAX_PASSES;
+constexpr int RS_SWEEP_SERIAL = RS_SWEEP_EXIT + RS_SWEEP_MAX_PASSES;
+constexpr int RS_SWEEP_CTL_WORDS = RS_SWEEP_SERIAL + 8;
 constexpr int RS_THREADS = 256;
 constexpr int RS_ITEMS = 8;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;

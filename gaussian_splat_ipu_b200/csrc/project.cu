@@ -134,7 +134,9 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
       const float radius = ceilf(3.f * sqrtf(max_ref(lambda1, lambda2)));
       const float bminx = px - radius, bminy = py - radius, bmaxx = px + radius, bmaxy = py + radius;
       const float ddx = bmaxx - bminx, ddy = bmaxy - bminy;
-      const bool within = sqrtf(ddx * ddx + ddy * ddy) < fp.guard;              // codelets.cpp:470
+      // codelets.cpp:470 `length(diagonal) < guard`: sqrtf(x) < guard  <=>  x < guard_sq (set_camera), also for
+      // x = +inf (false both ways) and NaN (false both ways); x is a sum of squares, never negative
+      const bool within = (ddx * ddx + ddy * ddy) < fp.guard_sq;
       rad = (bmaxx - bminx) * 0.5f;
       // a6: guard band, clip z < 0 (codelets.cpp:493), mean anchored by some tile
       // (Bounds2f::contains over the union of tiles, ipu_geometry.hpp:163-165)
@@ -142,7 +144,9 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
       drawn = within && (cz < 0.0f) && anchored;
       if (drawn) {
         // a7: converged lattice rectangle from Bounds2f::clip, ipu_geometry.hpp:133-155
-        c0 = (int)floorf(floorf(bminx) / fp.tile_w); c1 = (int)floorf(ceilf(bmaxx) / fp.tile_w);
+        // x / 32 and x * (1 / 32) are the same float (scaling by a power of two is exact)
+        if (fp.inv_tile_w != 0.0f) { c0 = (int)floorf(floorf(bminx) * fp.inv_tile_w); c1 = (int)floorf(ceilf(bmaxx) * fp.inv_tile_w); }
+        else { c0 = (int)floorf(floorf(bminx) / fp.tile_w); c1 = (int)floorf(ceilf(bmaxx) / fp.tile_w); }
         r0 = (int)floorf(floorf(bminy) / fp.tile_h); r1 = (int)floorf(ceilf(bmaxy) / fp.tile_h);
         int b0 = r0, b1 = r1;
         touched = clamp_rect(c0, c1, b0, b1, fp);

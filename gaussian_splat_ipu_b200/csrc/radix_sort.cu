@@ -18,6 +18,7 @@
 // per element per digit; digits are at most 7 bits wide (8 for the small per-slice depth sorts,
 // whose 128 KB of counters leave one CTA per SM).
 #include "gsplat_internal.h"
+#include <stdlib.h>
 
 namespace gsplat {
 
@@ -231,6 +232,8 @@ rs_scan_kernel(uint32_t *__restrict__ block_hist, uint32_t stride, const uint32_
 struct RsTail {
   uint32_t out_base[256];
   uint32_t wt[RS_WARPS + 1];
+  uint32_t tstart[257];     // rs_sweep_kernel: per-digit start inside the tile (+ the tile's length)
+  uint32_t ticket;          // rs_sweep_kernel: the tile this CTA works on
 };
 __host__ __device__ constexpr size_t rs_scatter_smem(int bits) {
   const size_t counters = (size_t)rs_counter_words(bits) * 4, staging = (size_t)RS_TILE * 8;
@@ -321,6 +324,221 @@ rs_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restri
   }
 }
 
+// ---- single-sweep passes ---------------------------------------------------------------------------
+// The three-kernel pass above costs three launches and three dependent round trips per digit; the
+// frame's two sorts per depth slice are 42 of its 57 launches, each a few microseconds long.  The
+// single-sweep form does a digit in ONE launch:
+//   rs_hist_all_kernel   once per sort: the digit totals of EVERY pass (the keys do not change
+//                        between passes, only their order), one read of the keys;
+//   rs_sweep_kernel      per digit: ranks a tile exactly as rs_scatter_kernel does, publishes the tile's
+//                        per-digit counts and obtains its per-digit offsets from the tiles before it by
+//                        decoupled look-back (one 64-bit word per (tile, digit): sort serial | pass,
+//                        flag, value — a word of another sort or pass reads as "not there yet", so
+//                        nothing is cleared between sorts).  Tiles are handed out by a ticket, so every
+//                        tile a CTA waits for belongs to a CTA that is already running.
+// Stable (tiles are ordered by the look-back, elements inside a tile by the ranking), so the result
+// is bit for bit the three-kernel sort's.  The control block cleans itself: the last CTA of a pass
+// to leave zeroes that pass's totals, ticket and exit counter.
+constexpr uint32_t SWEEP_FLAG_AGG = 1u, SWEEP_FLAG_INC = 2u;   // tile's own count / inclusive prefix
+constexpr int SWEEP_LOOKBACK = 8;                               // tiles examined per look-back step (loads in flight)
+__device__ __forceinline__ unsigned long long sweep_word(uint32_t tag, uint32_t flag, uint32_t value) {
+  return ((unsigned long long)tag << 34) | ((unsigned long long)flag << 32) | value;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Digit totals of all passes.  Shared-memory atomics; a thread merges runs of equal digits among its
+// RS_ITEMS consecutive keys first (sort B's keys — tile ids emitted Gaussian by Gaussian — and the top
+// digit of the depth keys are long runs of one value).  Passes above the key range are skipped, as
+// rs_sweep_kernel skips them.
+__global__ void __launch_bounds__(RS_THREADS)
+rs_hist_all_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ d_n, uint32_t cap, int begin_bit,
+                   int end_bit, int bpp, int passes, uint32_t *__restrict__ ctl, const uint32_t *__restrict__ key_range) {
+  __shared__ uint32_t hist[RS_SWEEP_MAX_PASSES * 256];
+  const uint32_t n = num_elems(d_n, cap);
+  if (n == 0) return;
+  const uint32_t tid = threadIdx.x;
+  if (blockIdx.x == 0 && tid == 0) ctl[RS_SWEEP_SERIAL] += 1u;     // read by the passes that follow
+  const uint32_t ntiles = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
+  if (blockIdx.x >= ntiles) return;
+  const uint32_t kbits = key_range ? key_range_bits(key_range) : 32u;
+  for (uint32_t k = tid; k < (uint32_t)passes * 256u; k += RS_THREADS) hist[k] = 0;
+  __syncthreads();
+  for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    uint32_t key[RS_ITEMS];
+    const uint32_t first = t * RS_TILE + tid * RS_ITEMS;
+    rs_load_blocked(keys, first, n, 0xffffffffu, key);
+    const uint32_t valid = first < n ? min((uint32_t)RS_ITEMS, n - first) : 0u;
+    for (int p = 0; p < passes; ++p) {
+      const int shift = begin_bit + p * bpp;
+      if (shift >= (int)kbits) break;
+      const int bits = (end_bit - shift) < bpp ? (end_bit - shift) : bpp;
+      const uint32_t mask = (1u << bits) - 1u;
+      uint32_t run_digit = 0, run = 0;
+#pragma unroll
+      for (int k = 0; k < RS_ITEMS; ++k) {
+        if ((uint32_t)k < valid) {
+          const uint32_t d = (key[k] >> shift) & mask;
+          if (run && d != run_digit) { atomicAdd(&hist[p * 256 + run_digit], run); run = 0; }
+          run_digit = d; ++run;
+        }
+      }
+      if (run) atomicAdd(&hist[p * 256 + run_digit], run);
+    }
+  }
+  __syncthreads();
+  for (uint32_t k = tid; k < (uint32_t)passes * 256u; k += RS_THREADS) {
+    const uint32_t v = hist[k];
+    if (v) atomicAdd(&ctl[RS_SWEEP_HIST + k], v);
+  }
+}
+
+template <int BITS>
+__global__ void __launch_bounds__(RS_THREADS, 3)
+rs_sweep_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+                uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
+                const uint32_t *__restrict__ d_n, uint32_t cap, int shift, int pass,
+                unsigned long long *__restrict__ tile_state, uint32_t *__restrict__ ctl,
+                const uint32_t *__restrict__ key_range, uint32_t backoff_ns) {
+  using G = RsGeom<BITS>;
+  constexpr uint32_t R = 1u << BITS;
+  extern __shared__ __align__(16) uint32_t rs_cnt[];
+  unsigned char *cbytes = reinterpret_cast<unsigned char *>(rs_cnt);
+  uint2 *stage = reinterpret_cast<uint2 *>(rs_cnt);
+  RsTail &tail = *reinterpret_cast<RsTail *>(cbytes + (rs_scatter_smem(BITS) - sizeof(RsTail)));
+  const uint32_t n = pass_elems(d_n, cap, key_range, shift);
+  if (n == 0) return;                       // skipped pass: its control words were never touched
+  const uint32_t ntiles = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t tid_off = rs_pad(tid) * 4u;
+  // global base of digit `tid`: exclusive scan of this pass's digit totals (rs_hist_all_kernel)
+  const uint32_t dt = tid <= G::MASK ? ctl[RS_SWEEP_HIST + pass * 256 + tid] : 0;
+  const uint32_t dbase = cta_excl_scan256(dt, tail.wt, lane, warp);
+  // words of this sort and pass only: anything else in tile_state reads as "not published yet"
+  const uint32_t tag = (ctl[RS_SWEEP_SERIAL] * (uint32_t)RS_SWEEP_MAX_PASSES + (uint32_t)pass) & 0x3fffffffu;
+
+  for (;;) {
+    if (tid == 0) tail.ticket = atomicAdd(&ctl[RS_SWEEP_TICKET + pass], 1u);
+    for (uint32_t k = tid * 2; k < G::WORDS; k += RS_THREADS * 2) *reinterpret_cast<uint2 *>(rs_cnt + k) = make_uint2(0, 0);
+    __syncthreads();
+    const uint32_t t = tail.ticket;
+    if (t >= ntiles) break;
+    const uint32_t tile_n = min((uint32_t)RS_TILE, n - t * RS_TILE);
+    uint32_t key[RS_ITEMS], val[RS_ITEMS], pos[RS_ITEMS];
+    const uint32_t first = t * RS_TILE + tid * RS_ITEMS;
+    rs_load_blocked(keys_in, first, n, 0xffffffffu, key);
+    if (vals_in) rs_load_blocked(vals_in, first, n, 0u, val);
+    else {   // first digit of sort A: value = element index
+#pragma unroll
+      for (int k = 0; k < RS_ITEMS; ++k) val[k] = first + k;
+    }
+    // count: pos[k] = how many earlier elements of THIS thread have the same digit
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+      unsigned short *c = reinterpret_cast<unsigned short *>(
+          cbytes + rs_counter_off<BITS>((key[k] >> shift) & G::MASK, tid_off));
+      const uint32_t r = *c;
+      *c = (unsigned short)(r + 1);
+      pos[k] = r;
+    }
+    __syncthreads();
+    {   // raking scan over all counter words, as in rs_scatter_kernel
+      const uint32_t sum = rs_rake<G::LANES, false>(rs_cnt, tid * G::LANES, 0u);
+      uint32_t total;
+      uint32_t run = cta_excl_scan256(sum, tail.wt, lane, warp, &total);
+      run += total << 16;
+      rs_rake<G::LANES, true>(rs_cnt, tid * G::LANES, run);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+      const unsigned short *c = reinterpret_cast<const unsigned short *>(
+          cbytes + rs_counter_off<BITS>((key[k] >> shift) & G::MASK, tid_off));
+      pos[k] += *c;
+    }
+    if (tid <= G::MASK) tail.tstart[tid] = *reinterpret_cast<const unsigned short *>(cbytes + rs_counter_off<BITS>(tid, 0u));
+    if (tid == 0) tail.tstart[R] = tile_n;      // the padding of the last tile ranks after every element
+    __syncthreads();   // counters are dead: the same memory now stages the sorted tile
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) stage[pos[k]] = make_uint2(key[k], val[k]);
+    if (tid <= G::MASK) {
+      // this tile's elements of digit `tid`, published; then the sum over the tiles before it
+      const uint32_t tstart = tail.tstart[tid], count = tail.tstart[tid + 1] - tstart;
+      unsigned long long *mine = tile_state + (size_t)t * R + tid;
+      uint32_t excl = 0;
+      if (t == 0) st_relaxed_u64(mine, sweep_word(tag, SWEEP_FLAG_INC, count));
+      else {
+        st_relaxed_u64(mine, sweep_word(tag, SWEEP_FLAG_AGG, count));
+        uint32_t p = t;                       // tiles [0, p) are still to be accounted for
+        bool found = false;
+        // the tile just before is examined alone first (in a long sort it usually holds its inclusive
+        // prefix already, and seven more loads would be wasted traffic); after that, SWEEP_LOOKBACK
+        // tiles per step with their loads in flight together
+        for (;;) {
+          const unsigned long long w0 = ld_relaxed_u64(tile_state + (size_t)(p - 1u) * R + tid);
+          const uint32_t flag = (uint32_t)(w0 >> 32) & 3u;
+          if ((uint32_t)(w0 >> 34) == tag && flag != 0) {
+            excl += (uint32_t)w0;
+            --p;
+            found = flag == SWEEP_FLAG_INC;
+            break;
+          }
+          if (backoff_ns) __nanosleep(backoff_ns);
+        }
+        while (!found) {
+          unsigned long long w[SWEEP_LOOKBACK];
+#pragma unroll
+          for (int j = 0; j < SWEEP_LOOKBACK; ++j)
+            w[j] = p > (uint32_t)j ? ld_relaxed_u64(tile_state + (size_t)(p - 1u - j) * R + tid) : 0ull;
+          const uint32_t p_before = p;
+#pragma unroll
+          for (int j = 0; j < SWEEP_LOOKBACK; ++j) {
+            if (found || p == 0) break;
+            const uint32_t flag = (uint32_t)(w[j] >> 32) & 3u;
+            if ((uint32_t)(w[j] >> 34) != tag || flag == 0) break;      // not published yet: read again from here
+            excl += (uint32_t)w[j];
+            --p;
+            found = flag == SWEEP_FLAG_INC;
+          }
+          // nothing new: the tile before is still ranking.  Do not hammer L2 (and the issue slots of
+          // whatever shares the SM) while it does
+          if (!found && p == p_before && backoff_ns) __nanosleep(backoff_ns);
+        }
+        st_relaxed_u64(mine, sweep_word(tag, SWEEP_FLAG_INC, excl + count));
+      }
+      tail.out_base[tid] = dbase + excl - tstart;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+      const uint32_t q = k * RS_THREADS + tid;
+      if (q < tile_n) {
+        const uint2 kv = stage[q];
+        const uint32_t dst = tail.out_base[(kv.x >> shift) & G::MASK] + q;
+        keys_out[dst] = kv.x;
+        vals_out[dst] = kv.y;
+      }
+    }
+    __syncthreads();
+  }
+  // the last CTA of the pass to leave puts the control words back to zero for the next sort
+  if (tid == 0) {
+    __threadfence();
+    if (atomicAdd(&ctl[RS_SWEEP_EXIT + pass], 1u) + 1u == gridDim.x) tail.ticket = 0xffffffffu;
+  }
+  __syncthreads();
+  if (tail.ticket == 0xffffffffu) {
+    for (uint32_t k = tid; k < 256u; k += RS_THREADS) ctl[RS_SWEEP_HIST + pass * 256 + k] = 0u;
+    if (tid == 0) { ctl[RS_SWEEP_TICKET + pass] = 0u; ctl[RS_SWEEP_EXIT + pass] = 0u; }
+  }
+}
+
 void sort_plan(int nbits, int &passes, int &bits_per_pass, int max_bits) {
   if (nbits < 1) nbits = 1;
   if (max_bits < 1 || max_bits > 8) max_bits = RS_MAX_BITS;
@@ -340,9 +558,25 @@ static void launch_pass(SortBuffers &sb, int cur, bool identity, const uint32_t 
       sb.block_hist, sb.max_tiles, sb.digit_totals, key_range);
 }
 
+// pause of a look-back that found nothing new (ns; GSPLAT_SORT_BACKOFF_NS for experiments)
+static uint32_t sweep_backoff_ns() {
+  static const uint32_t ns = [] { const char *e = getenv("GSPLAT_SORT_BACKOFF_NS"); return e ? (uint32_t)atoi(e) : 100u; }();
+  return ns;
+}
+
+template <int BITS>
+static void launch_sweep(SortBuffers &sb, int cur, bool identity, const uint32_t *d_n, int shift, int pass, uint32_t grid,
+                         const uint32_t *key_range, cudaStream_t st) {
+  rs_sweep_kernel<BITS><<<grid, RS_THREADS, rs_scatter_smem(BITS), st>>>(
+      sb.keys[cur], identity ? nullptr : sb.vals[cur], sb.keys[cur ^ 1], sb.vals[cur ^ 1], d_n, sb.capacity, shift, pass,
+      sb.tile_state, sb.sweep_ctl, key_range, sweep_backoff_ns());
+}
+
 template <int BITS> static cudaError_t sort_attr() {
   cudaError_t e = cudaFuncSetAttribute(rs_scatter_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)rs_scatter_smem(BITS));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(rs_sweep_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_scatter_smem(BITS));
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(rs_hist_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)rs_counter_words(BITS) * 4);
@@ -365,6 +599,30 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
   int passes, bpp;
   sort_plan(end_bit - begin_bit, passes, bpp, max_bits);
   const uint32_t grid = ntiles < (uint32_t)RS_GRID ? ntiles : (uint32_t)RS_GRID;
+  if (sb.tile_state && sb.sweep_ctl && passes <= RS_SWEEP_MAX_PASSES) {
+    // single-sweep form: the digit totals of all passes in one launch, then one launch per digit
+    ++g_launches;
+    rs_hist_all_kernel<<<grid, RS_THREADS, 0, st>>>(sb.keys[0], d_n, sb.capacity, begin_bit, end_bit, bpp, passes,
+                                                     sb.sweep_ctl, key_range);
+    for (int p = 0; p < passes; ++p) {
+      const int shift = begin_bit + p * bpp;
+      const int bits = (end_bit - shift) < bpp ? (end_bit - shift) : bpp;
+      const bool ident = p == 0 && identity_vals;
+      ++g_launches;
+      switch (bits) {
+        case 1: launch_sweep<1>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
+        case 2: launch_sweep<2>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
+        case 3: launch_sweep<3>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
+        case 4: launch_sweep<4>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
+        case 5: launch_sweep<5>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
+        case 6: launch_sweep<6>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
+        case 7: launch_sweep<7>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
+        default: launch_sweep<8>(sb, cur, ident, d_n, shift, p, grid < 148u ? grid : 148u, key_range, st); break;
+      }
+      cur ^= 1;
+    }
+    return cur;
+  }
   for (int p = 0; p < passes; ++p) {
     const int shift = begin_bit + p * bpp;
     const int bits = (end_bit - shift) < bpp ? (end_bit - shift) : bpp;
