@@ -71,7 +71,7 @@ constexpr int BLEND_MAX_WARPS = 20;                  // consumer warps of an und
 // runs the exact chain for the lanes it reaches: 4 % slower than the per-pixel sets below) and 64
 // staged entries per consumer turn (one phase B over two chunks: K5 0.373-0.379 ms against 0.348-0.350).
 // 1 = phase A walks a compacted list of the hit lanes, 0 = find-first-set on the hit ballot.
-// Measured (profiles/ab_k5_r3a.txt): the list is SLOWER, K5 0.331 ms against 0.314 (the store, the warp
+// Measured (profiles/ab_k5_r2c.txt): the list is SLOWER, K5 0.331 ms against 0.314 (the store, the warp
 // barrier and the dependent load cost more than the uniform-datapath bit walk): default 0.
 #ifndef GSPLAT_BLEND_HITLIST
 #define GSPLAT_BLEND_HITLIST 0

@@ -543,9 +543,11 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     if (const char *e = std::getenv("GSPLAT_K5_SPLIT")) split = std::atoi(e);
     if (split != 1 && split != 2 && split != 4) split = 2;
     ctx->blend_split = split;
-    int later = 4;
+    // later slices: also two strips (measured with this round's K5, profiles/ab_k5_r2e.txt: 2 strips 1603,
+    // 4 strips 1582, 1 strip 1592 frames/s; the earlier K5 preferred 4)
+    int later = 2;
     if (const char *e = std::getenv("GSPLAT_K5_SPLIT_LATER")) later = std::atoi(e);
-    if (later != 1 && later != 2 && later != 4) later = 4;
+    if (later != 1 && later != 2 && later != 4) later = 2;
     ctx->blend_split_later = later;
     if (const char *e = std::getenv("GSPLAT_GRAPHS")) ctx->use_graphs = std::atoi(e) != 0;
     CUC(cudaMalloc(&ctx->tstate, sizeof(float) * px));

@@ -74,8 +74,8 @@ typedef struct gsplat_config {
                          /* or 1 when collect_timings / debug_records are set.  Costs one set of    */
                          /* buffers (about 250 bytes per Gaussian) per frame in flight.             */
 } gsplat_config;
-#define GSPLAT_MAX_CONCURRENT_FRAMES 4
-#define GSPLAT_DEFAULT_CONCURRENT_FRAMES 3
+#define GSPLAT_MAX_CONCURRENT_FRAMES 8
+#define GSPLAT_DEFAULT_CONCURRENT_FRAMES 4
 #define GSPLAT_MAX_DEPTH_SLICES 8
 #define GSPLAT_DEFAULT_DEPTH_SLICES 2
 
