@@ -232,7 +232,13 @@ __device__ __forceinline__ bool blend_exact_pred(bool on, const float4 b, const 
 // FIRST: start from T = 1, C = 0.  LAST: no state is saved.
 // blockDim = (consumer warps + 1) * 32; the last warp is the producer.
 template <bool COUNT, bool FIRST, bool LAST>
+// GSPLAT_BLEND_MINBLOCKS=3 caps K5 at 32 registers (5 CTAs per SM instead of 4).  Measured
+// (profiles/ab_k5_r2e.txt): K5 alone gets slower (0.308 -> 0.341 ms), four frames in flight gain 0.7 %: not taken.
+#ifdef GSPLAT_BLEND_MINBLOCKS
+__global__ void __launch_bounds__((BLEND_MAX_WARPS + 1) * 32, GSPLAT_BLEND_MINBLOCKS)
+#else
 __global__ void __launch_bounds__((BLEND_MAX_WARPS + 1) * 32)
+#endif
 blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
              int tiles_across, const uint32_t *__restrict__ band, int full_tile_h, int split_log2, float4 *__restrict__ fb,
              float *__restrict__ tstate, TileState ts, const uint32_t *__restrict__ order,
