@@ -32,7 +32,9 @@ for r in rows[2:]:
             pass
     seq.append((name, b, float(r[it].replace(",", "")) * tmult[units[it]], extra))
 starts = [i for i, s in enumerate(seq) if s[0].startswith("project_kernel")]
-a, b = starts[-2], starts[-1]          # the last complete frame of the capture
+# the last complete frame of the capture (project_kernel .. next project_kernel, or .. the end of the
+# capture when it stops after a frame's last blend_kernel)
+a, b = (starts[-2], starts[-1]) if len(starts) > 1 else (starts[0], len(seq))
 frame = seq[a:b]
 
 STAGES = [("k1_project", r"project_kernel|tile_count|depth_quantile"), ("k3a_sort_depth", r"select_kernel|live_sat|rs_\w+<[7854]>"),
