@@ -187,7 +187,7 @@ class B200Splatter:
             cfg.band_row_begin, cfg.band_row_end = band
         cfg.collect_timings, cfg.debug_records, cfg.dup_capacity = int(collect_timings), int(debug_records), dup_capacity
         cfg.depth_slices = int(depth_slices)   # 0 = library default; 1 = complete (reference) lists
-        cfg.concurrent_frames = int(concurrent_frames)   # 0 = library default (2 frames in flight on the device)
+        cfg.concurrent_frames = int(concurrent_frames)   # 0 = library default (GSPLAT_DEFAULT_CONCURRENT_FRAMES = 4)
         self.cfg = cfg
         self.h = _vp()
         rc = self.lib.gsplat_create(C.byref(cfg), C.byref(self.h))

@@ -65,14 +65,16 @@ typedef struct gsplat_config {
                          /* 1 = one slice: every tile's list is the reference's complete list.  */
                          /* 0 = default (GSPLAT_DEFAULT_DEPTH_SLICES).  Framebuffer and counts   */
                          /* do not depend on it; lists are exact prefixes of the reference's.   */
-  int concurrent_frames; /* frames the context keeps in flight on the device (1..4): the frame is a */
+  int concurrent_frames; /* frames the context keeps in flight on the device (1..8): the frame is a */
                          /* chain of short, latency-bound launches, so consecutive frames run on    */
                          /* separate streams with their own working buffers ("lanes", round-robin)  */
                          /* and interleave on the SMs.  Every call that reads a result refers to    */
                          /* the frame rendered last; the depth_slices = 0 choice is then made for   */
                          /* all lanes from frames run alone.  0 = default: GSPLAT_DEFAULT_CONCURRENT_FRAMES, */
                          /* or 1 when collect_timings / debug_records are set.  Costs one set of    */
-                         /* buffers (about 250 bytes per Gaussian) per frame in flight.             */
+                         /* buffers (about 250 bytes per Gaussian) per frame in flight.  A context  */
+                         /* with ONE frame in flight sorts with single-sweep passes (33 launches a  */
+                         /* frame instead of 57: lower latency).                */
 } gsplat_config;
 #define GSPLAT_MAX_CONCURRENT_FRAMES 8
 #define GSPLAT_DEFAULT_CONCURRENT_FRAMES 4
