@@ -467,10 +467,24 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
             smask |= (q0 <= b0.w ? 1u << l0 : 0u) | (q1 <= b1.w ? 1u << l1 : 0u);
           }
           if (done) smask = 0;
+          if (COUNT) {   // probes: chunks with a hit, hit entries, hit entries no live pixel passes the pre-test for
+            uint32_t hm = masks[h], dead = 0;
+            while (hm) { const uint32_t l = __ffs(hm) - 1; hm &= hm - 1; dead += __any_sync(0xffffffffu, (smask >> l) & 1u) ? 0u : 1u; }
+            const uint32_t live = __popc(__ballot_sync(0xffffffffu, !done));
+            if (lane == 0) {
+              atomicAdd(&pair_counters[2], 1ull); atomicAdd(&pair_counters[3], (unsigned long long)__popc(masks[h])); atomicAdd(&pair_counters[4], (unsigned long long)dead);
+              if (live == 32) { atomicAdd(&pair_counters[7], (unsigned long long)__popc(masks[h])); atomicAdd(&pair_counters[8], (unsigned long long)dead); }
+              atomicAdd(&pair_counters[9], (unsigned long long)live);
+            }
+          }
           // Phase B, one pixel per lane: every lane walks ITS OWN entries in list order through the
           // exact chain, so a turn of the loop blends up to 32 different (pixel, entry) pairs instead of
           // one entry against the few pixels it reaches; turns = the longest per-pixel set.
           while (__any_sync(0xffffffffu, smask != 0)) {
+            if (COUNT) {   // probes: phase B turns and the lanes busy in them
+              const uint32_t busy = __popc(__ballot_sync(0xffffffffu, smask != 0));
+              if (lane == 0) { atomicAdd(&pair_counters[5], 1ull); atomicAdd(&pair_counters[6], (unsigned long long)busy); }
+            }
 #if GSPLAT_BLEND_PRED
             // straight-line turn: lanes whose set is empty run a stale entry with `on` false.  With
             // ~15 lanes busy per turn (measured) a warp-level skip almost never happens, and the
@@ -517,8 +531,8 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
       }
       if (lane == 0) {
         atomicAdd(&pair_counters[0], n_visit); atomicAdd(&pair_counters[1], n_blend);
-        atomicAdd(&pair_counters[2 + 2 * (size_t)tile + 1], n_visit);            // per-tile profile tap
-        atomicAdd(&pair_counters[2 + 2 * (size_t)tile], (unsigned long long)(clock64() - t_begin) / NW);
+        atomicAdd(&pair_counters[K5_TILE_WORDS0 + 2 * (size_t)tile + 1], n_visit);            // per-tile profile tap
+        atomicAdd(&pair_counters[K5_TILE_WORDS0 + 2 * (size_t)tile], (unsigned long long)(clock64() - t_begin) / NW);
       }
     }
     if (valid) fb[px] = make_float4(Cr, Cg, Cb, Ca);

@@ -213,6 +213,10 @@ constexpr uint32_t DEPTH_KEY_CULLED = 0xffffffffu;
 constexpr uint32_t RECT_EMPTY = 1u;   // {lo = 1, hi = 0}: the rectangle of a Gaussian that is not drawn
 
 constexpr int K1_THREADS = 256;
+// counting re-run of K5 (gsplat_profile_tiles): words [0] visited pairs, [1] blended pairs, then
+// K5_PROBE_WORDS experiment counters, then per tile {cycles, visited pairs}
+constexpr int K5_PROBE_WORDS = 8;
+constexpr int K5_TILE_WORDS0 = 2 + K5_PROBE_WORDS;
 // K1 (and the parity inject) write the frame's band {row_begin, row_end} at this word offset from
 // their drawn counter; tile_order and K5 read it there (`band` arguments below)
 constexpr int BAND_WORD_OFFSET = 2;
