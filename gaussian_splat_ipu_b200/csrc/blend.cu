@@ -234,17 +234,11 @@ __device__ __forceinline__ bool blend_exact_pred(bool on, const float4 b, const 
 // FIRST: start from T = 1, C = 0.  LAST: no state is saved.
 // blockDim = (consumer warps + 1) * 32; the last warp is the producer.
 template <bool COUNT, bool FIRST, bool LAST>
-// GSPLAT_BLEND_MINBLOCKS=3 caps K5 at 32 registers (5 CTAs per SM instead of 4).  Measured
-// (profiles/ab_k5_r2e.txt): K5 alone gets slower (0.308 -> 0.341 ms), four frames in flight gain 0.7 %: not taken.
-#ifdef GSPLAT_BLEND_MINBLOCKS
-__global__ void __launch_bounds__((BLEND_MAX_WARPS + 1) * 32, GSPLAT_BLEND_MINBLOCKS)
-#else
-__global__ void __launch_bounds__((BLEND_MAX_WARPS + 1) * 32)
-#endif
-blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
-             int tiles_across, const uint32_t *__restrict__ band, int full_tile_h, int split_log2, float4 *__restrict__ fb,
-             float *__restrict__ tstate, TileState ts, const uint32_t *__restrict__ order,
-             unsigned long long *__restrict__ pair_counters) {
+__device__ __forceinline__ void
+blend_body(const Projected &p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
+           int tiles_across, const uint32_t *__restrict__ band, int full_tile_h, int split_log2, float4 *__restrict__ fb,
+           float *__restrict__ tstate, const TileState &ts, const uint32_t *__restrict__ order,
+           unsigned long long *__restrict__ pair_counters) {
   extern __shared__ __align__(128) unsigned char blend_smem_raw[];
   BlendSmem &sm = *reinterpret_cast<BlendSmem *>(blend_smem_raw);
   const long long t_begin = COUNT ? clock64() : 0;
@@ -547,6 +541,30 @@ blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__rest
   }
 }
 
+// The two entry points of the body.  blend_kernel: any CTA size up to a whole tile (21 warps), 40
+// registers.  blend_kernel_wide: CTAs of at most 11 warps (two or four strips per tile) with the 53
+// registers the body asks for, 3 CTAs per SM instead of 4.  Measured (profiles/ab_k5_r2e.txt): the wide
+// form is the faster K5 when a frame runs alone (0.292 against 0.311 ms) and the slower one when
+// several frames are in flight (1578 against 1608 frames/s: residency counts there), so a context that
+// renders one frame at a time launches the wide form and the lanes of a dispatcher the other.
+// (Capping at 32 registers, 5 CTAs per SM: K5 alone 0.341 ms, frames in flight +0.7 %: not taken.)
+constexpr int BLEND_WIDE_WARPS = 11;
+template <bool COUNT, bool FIRST, bool LAST>
+__global__ void __launch_bounds__((BLEND_MAX_WARPS + 1) * 32)
+blend_kernel(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
+             int tiles_across, const uint32_t *__restrict__ band, int full_tile_h, int split_log2, float4 *__restrict__ fb,
+             float *__restrict__ tstate, TileState ts, const uint32_t *__restrict__ order,
+             unsigned long long *__restrict__ pair_counters) {
+  blend_body<COUNT, FIRST, LAST>(p, vals, ranges, tiles_across, band, full_tile_h, split_log2, fb, tstate, ts, order, pair_counters);
+}
+template <bool FIRST, bool LAST>
+__global__ void __launch_bounds__(BLEND_WIDE_WARPS * 32, 3)
+blend_kernel_wide(Projected p, const uint32_t *__restrict__ vals, const uint2 *__restrict__ ranges,
+                  int tiles_across, const uint32_t *__restrict__ band, int full_tile_h, int split_log2, float4 *__restrict__ fb,
+                  float *__restrict__ tstate, TileState ts, const uint32_t *__restrict__ order) {
+  blend_body<false, FIRST, LAST>(p, vals, ranges, tiles_across, band, full_tile_h, split_log2, fb, tstate, ts, order, nullptr);
+}
+
 // ---- launch order of the tiles: longest list first ---------------------------------------------
 // CTAs are dispatched in blockIdx order; a tile with a long list that starts late leaves the other
 // SMs idle at the end of the launch.  One CTA buckets the band's tiles by list length (power-of-two
@@ -622,21 +640,34 @@ static size_t blend_smem_bytes() {
 
 template <bool COUNT, bool FIRST, bool LAST>
 static void launch_blend_t(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                           const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split,
+                           const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split, bool wide,
                            const uint32_t *order, unsigned long long *pair_counters, cudaStream_t st) {
   const int rows = fp.tiles_down;   // launch geometry for the whole image: the band is only known on the device
   const int full_h = (int)fp.tile_h;
   const int split_log2 = split >= 4 ? 2 : (split >= 2 ? 1 : 0);  // split is 1, 2 or 4
   const int part_w = 32 >> split_log2;                            // columns per CTA
   const int warps = (part_w / 8) * ((full_h + 3) / 4);           // one consumer warp per 8 x 4 pixel block
+  const unsigned grid = (unsigned)(rows * fp.tiles_across) << split_log2;
   ++g_launches;
-  blend_kernel<COUNT, FIRST, LAST><<<(rows * fp.tiles_across) << split_log2, (warps + 1) * 32, blend_smem_bytes(), st>>>(
+  if constexpr (!COUNT) {
+    if (wide && warps + 1 <= BLEND_WIDE_WARPS) {
+      blend_kernel_wide<FIRST, LAST><<<grid, (warps + 1) * 32, blend_smem_bytes(), st>>>(
+          p, sorted_vals, ranges, fp.tiles_across, band, full_h, split_log2, fb_tiled, tstate, ts, order);
+      return;
+    }
+  }
+  blend_kernel<COUNT, FIRST, LAST><<<grid, (warps + 1) * 32, blend_smem_bytes(), st>>>(
       p, sorted_vals, ranges, fp.tiles_across, band, full_h, split_log2, fb_tiled, tstate, ts, order, pair_counters);
 }
 
 template <bool COUNT, bool FIRST, bool LAST> static cudaError_t blend_attr() {
-  return cudaFuncSetAttribute(blend_kernel<COUNT, FIRST, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)blend_smem_bytes());
+  cudaError_t e = cudaFuncSetAttribute(blend_kernel<COUNT, FIRST, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)blend_smem_bytes());
+  if constexpr (!COUNT) {
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(blend_kernel_wide<FIRST, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)blend_smem_bytes());
+  }
+  return e;
 }
 // Dynamic shared memory opt-in of every K5 variant on the CURRENT device (the attribute belongs to
 // the device's context: gsplat_create runs this once per device).
@@ -651,10 +682,10 @@ cudaError_t setup_blend_kernels() {
 }
 
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                  const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split, uint32_t *order,
-                  bool first, bool last, unsigned long long *pair_counters, cudaStream_t st) {
+                  const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split, bool wide,
+                  uint32_t *order, bool first, bool last, unsigned long long *pair_counters, cudaStream_t st) {
   launch_tile_order(ranges, fp, band, ts.tile_done, first, order, st);
-#define GSPLAT_BLEND(C, F, L) launch_blend_t<C, F, L>(p, sorted_vals, ranges, fp, band, fb_tiled, tstate, ts, split, order, pair_counters, st)
+#define GSPLAT_BLEND(C, F, L) launch_blend_t<C, F, L>(p, sorted_vals, ranges, fp, band, fb_tiled, tstate, ts, split, wide, order, pair_counters, st)
   if (pair_counters) {
     if (first) { if (last) GSPLAT_BLEND(true, true, true); else GSPLAT_BLEND(true, true, false); }
     else { if (last) GSPLAT_BLEND(true, false, true); else GSPLAT_BLEND(true, false, false); }

@@ -150,6 +150,7 @@ struct gsplat_ctx {
   TileState ts{};                  // per tile / per part: every pixel has stopped
   int blend_split = 1;             // K5 CTAs per semantic tile in the first depth slice
   int blend_split_later = 1;       // ... and in the later slices (fewer live tiles: narrower parts fill the SMs)
+  bool blend_wide = false;         // K5 in its 53-register form (one frame at a time), see blend.cu
   // frame graphs: [0] one slice, [1] sliced; dropped whenever buffers, scene or band change
   FrameGraph graphs[2];
   bool use_graphs = true;          // GSPLAT_GRAPHS=0 disables (eager launches)
@@ -457,6 +458,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
           return rc;
         }
         lane->is_lane = true;
+        if (!std::getenv("GSPLAT_K5_WIDE")) lane->blend_wide = false;   // several frames in flight: residency counts (blend.cu)
         outer->lanes.push_back(lane);
       }
       cudaSetDevice(cfg->device);
@@ -549,6 +551,8 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     if (const char *e = std::getenv("GSPLAT_K5_SPLIT_LATER")) later = std::atoi(e);
     if (later != 1 && later != 2 && later != 4) later = 2;
     ctx->blend_split_later = later;
+    ctx->blend_wide = true;     // lanes of a dispatcher: switched off when the lane is adopted (gsplat_create)
+    if (const char *e = std::getenv("GSPLAT_K5_WIDE")) ctx->blend_wide = std::atoi(e) != 0;
     if (const char *e = std::getenv("GSPLAT_GRAPHS")) ctx->use_graphs = std::atoi(e) != 0;
     CUC(cudaMalloc(&ctx->tstate, sizeof(float) * px));
   }

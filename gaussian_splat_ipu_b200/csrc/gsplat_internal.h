@@ -354,11 +354,12 @@ struct TileState {
 };
 constexpr int BLEND_MAX_SPLIT = 8;
 inline size_t tile_state_bytes(int tiles) { return (size_t)tiles * (1 + BLEND_MAX_SPLIT + 4) + 16; }
+// `wide`: the 53-register form of K5 (a context that renders one frame at a time; blend.cu).
 // `band`: device words {row_begin, row_end} of the frame's tile-row band (written by K1); the grid
 // covers every tile of the image and the CTAs beyond the band leave at once.
 void launch_blend(const Projected &p, const uint32_t *sorted_vals, const uint2 *ranges, const FrameParams &fp,
-                  const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split, uint32_t *order,
-                  bool first, bool last, unsigned long long *pair_counters, cudaStream_t st);
+                  const uint32_t *band, float4 *fb_tiled, float *tstate, const TileState &ts, int split, bool wide,
+                  uint32_t *order, bool first, bool last, unsigned long long *pair_counters, cudaStream_t st);
 
 // a10: tiled f32 RGBA -> de-tiled BGR8 rows.
 void launch_bgr8(const float4 *fb_tiled, uint8_t *bgr, int W, int H, int tile_w, int tile_h,
