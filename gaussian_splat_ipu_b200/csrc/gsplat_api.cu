@@ -551,7 +551,12 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     if (const char *e = std::getenv("GSPLAT_K5_SPLIT_LATER")) later = std::atoi(e);
     if (later != 1 && later != 2 && later != 4) later = 2;
     ctx->blend_split_later = later;
-    ctx->blend_wide = true;     // lanes of a dispatcher: switched off when the lane is adopted (gsplat_create)
+    // K5's 53-register form (blend.cu): for a frame that runs alone, and only while the launch is a few
+    // waves of CTAs — its end, a handful of long-running CTAs, is then what counts (6 M @1080p: 0.311 ->
+    // 0.292 ms; 1 M: 0.186 -> 0.171).  At 4K (26 k CTAs) the launch is throughput-bound and the 40-register
+    // form with 4 CTAs per SM wins (0.66 against 0.69 ms).  Lanes of a dispatcher: switched off when the
+    // lane is adopted (gsplat_create).
+    ctx->blend_wide = (size_t)ctx->num_tiles * (size_t)split <= (size_t)148 * 64;
     if (const char *e = std::getenv("GSPLAT_K5_WIDE")) ctx->blend_wide = std::atoi(e) != 0;
     if (const char *e = std::getenv("GSPLAT_GRAPHS")) ctx->use_graphs = std::atoi(e) != 0;
     CUC(cudaMalloc(&ctx->tstate, sizeof(float) * px));
