@@ -151,6 +151,7 @@ struct gsplat_ctx {
   int blend_split = 1;             // K5 CTAs per semantic tile in the first depth slice
   int blend_split_later = 1;       // ... and in the later slices (fewer live tiles: narrower parts fill the SMs)
   bool blend_wide = false;         // K5 in its 53-register form (one frame at a time), see blend.cu
+  bool k1_dense = true;            // K1 at 32 registers / 64 warps per SM (one frame at a time), see project.cu
   // frame graphs: [0] one slice, [1] sliced; dropped whenever buffers, scene or band change
   FrameGraph graphs[2];
   bool use_graphs = true;          // GSPLAT_GRAPHS=0 disables (eager launches)
@@ -459,6 +460,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
         }
         lane->is_lane = true;
         if (!std::getenv("GSPLAT_K5_WIDE")) lane->blend_wide = false;   // several frames in flight: residency counts (blend.cu)
+        if (!std::getenv("GSPLAT_K1_DENSE")) lane->k1_dense = false;    // ... and K1 must leave room beside it (project.cu)
         outer->lanes.push_back(lane);
       }
       cudaSetDevice(cfg->device);
@@ -558,6 +560,7 @@ int gsplat_create(const gsplat_config *cfg, gsplat_ctx **out) {
     // lane is adopted (gsplat_create).
     ctx->blend_wide = (size_t)ctx->num_tiles * (size_t)split <= (size_t)148 * 64;
     if (const char *e = std::getenv("GSPLAT_K5_WIDE")) ctx->blend_wide = std::atoi(e) != 0;
+    if (const char *e = std::getenv("GSPLAT_K1_DENSE")) ctx->k1_dense = std::atoi(e) != 0;
     if (const char *e = std::getenv("GSPLAT_GRAPHS")) ctx->use_graphs = std::atoi(e) != 0;
     CUC(cudaMalloc(&ctx->tstate, sizeof(float) * px));
   }

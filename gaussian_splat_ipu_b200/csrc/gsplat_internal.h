@@ -227,9 +227,9 @@ void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st);
 void launch_cov3(const SceneSoA &scene, float scale_div, cudaStream_t st);
 // K1: writes Projected; drawn_counter += number of drawn Gaussians (V).
 void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *drawn_counter,
-                    float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st);
-// Address of K1's kernel (to find its node in a captured frame graph and refresh its camera argument).
-const void *project_kernel_address();
+                    float *dbg_rec8, int32_t *dbg_rect4, bool dense, cudaStream_t st);
+// Is `func` one of K1's kernels (to find its node in a captured frame graph and refresh its camera argument)?
+bool is_project_kernel(const void *func);
 // Debug/parity entry: fill depth key / rect from caller-supplied projected inputs.
 void launch_inject(const float *depth, const int32_t *rect4, const uint8_t *drawn, uint32_t n,
                    const FrameParams &fp, Projected out, uint32_t *drawn_counter, cudaStream_t st);

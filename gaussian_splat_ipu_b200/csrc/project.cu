@@ -61,9 +61,9 @@ __device__ __forceinline__ uint32_t clamp_rect(int &c0, int &c1, int &r0, int &r
   return (uint32_t)(c1 - c0 + 1) * (uint32_t)(b1 - b0 + 1);
 }
 
-__global__ void __launch_bounds__(K1_THREADS)
-project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__ drawn_counter,
-               float *__restrict__ dbg_rec8, int32_t *__restrict__ dbg_rect4) {
+__device__ __forceinline__ void
+project_body(const SceneSoA &s, const FrameParams &fp, const Projected &out, uint32_t *__restrict__ drawn_counter,
+             float *__restrict__ dbg_rec8, int32_t *__restrict__ dbg_rect4) {
   // the frame's tile-row band, for the kernels behind K1 in the (captured) frame: only K1's
   // argument block is refreshed per frame, so a band change needs no re-capture (drawn_counter is
   // word SC_V of the frame scalars; the band words sit at BAND_WORD_OFFSET from it)
@@ -209,6 +209,22 @@ project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__
   if (threadIdx.x == 0 && nd) atomicAdd(drawn_counter, nd);
 }
 
+// Two entry points of K1's body.  project_kernel: 40 registers, 6 CTAs per SM.  project_kernel_dense:
+// capped at 32 registers (a few spilled words), 8 CTAs = all 64 warps per SM: K1 alone 0.150 -> 0.143 ms
+// (0.85 of HBM), but it then leaves no room for another lane's kernels beside it — with several
+// frames in flight 1504 against 1604 frames/s (profiles/ab_k5_r2e.txt).  So a context that renders one
+// frame at a time launches the dense form, the lanes of a dispatcher the other.
+__global__ void __launch_bounds__(K1_THREADS)
+project_kernel(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__ drawn_counter,
+               float *__restrict__ dbg_rec8, int32_t *__restrict__ dbg_rect4) {
+  project_body(s, fp, out, drawn_counter, dbg_rec8, dbg_rect4);
+}
+__global__ void __launch_bounds__(K1_THREADS, 8)
+project_kernel_dense(SceneSoA s, FrameParams fp, Projected out, uint32_t *__restrict__ drawn_counter,
+                     float *__restrict__ dbg_rec8, int32_t *__restrict__ dbg_rect4) {
+  project_body(s, fp, out, drawn_counter, dbg_rec8, dbg_rect4);
+}
+
 // Parity entry (gsplat_bin_projected): take depth / rect / drawn from the caller instead of K1.
 __global__ void __launch_bounds__(K1_THREADS)
 inject_kernel(const float *__restrict__ depth, const int32_t *__restrict__ rect4,
@@ -306,13 +322,16 @@ void launch_aos_to_soa(const float *aos16, SceneSoA scene, cudaStream_t st) {
   aos_to_soa_kernel<<<ceil_div(scene.n, 256), 256, 0, st>>>(reinterpret_cast<const float4 *>(aos16), scene);
 }
 
-const void *project_kernel_address() { return reinterpret_cast<const void *>(&project_kernel); }
+bool is_project_kernel(const void *func) {
+  return func == reinterpret_cast<const void *>(&project_kernel) || func == reinterpret_cast<const void *>(&project_kernel_dense);
+}
 
 void launch_project(const SceneSoA &scene, const FrameParams &fp, Projected out, uint32_t *drawn_counter,
-                    float *dbg_rec8, int32_t *dbg_rect4, cudaStream_t st) {
+                    float *dbg_rec8, int32_t *dbg_rect4, bool dense, cudaStream_t st) {
   ++g_launches;   // an empty scene still launches one CTA: K1 publishes the frame's band
-  project_kernel<<<scene.n ? ceil_div(scene.n, K1_THREADS) : 1, K1_THREADS, 0, st>>>(scene, fp, out, drawn_counter, dbg_rec8,
-                                                                      dbg_rect4);
+  const int grid = scene.n ? ceil_div(scene.n, K1_THREADS) : 1;
+  if (dense) project_kernel_dense<<<grid, K1_THREADS, 0, st>>>(scene, fp, out, drawn_counter, dbg_rec8, dbg_rect4);
+  else project_kernel<<<grid, K1_THREADS, 0, st>>>(scene, fp, out, drawn_counter, dbg_rec8, dbg_rect4);
 }
 
 void launch_inject(const float *depth, const int32_t *rect4, const uint8_t *drawn, uint32_t n,
