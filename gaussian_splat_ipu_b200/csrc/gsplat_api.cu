@@ -236,13 +236,17 @@ int alloc_sort(gsplat_ctx *ctx, SortBuffers &s, size_t capacity) {
   CU(cudaMalloc(&s.block_hist, (size_t)256 * s.max_tiles * sizeof(uint32_t)));
   CU(cudaMalloc(&s.digit_totals, 256 * sizeof(uint32_t)));
   CU(cudaMemset(s.digit_totals, 0, 256 * sizeof(uint32_t)));
-  // Which form of the sort passes (radix_sort.cu).  Measured on the 6 M bench frame (profiles/ab_sort_r2.txt):
-  // the single-sweep passes take 50 us off a frame's latency (57 -> 33 launches) but their waiting
-  // CTAs cost a context with several frames in flight 1 % of its throughput, so a context that
-  // renders one frame at a time gets them and the lanes of a dispatcher keep the three-kernel passes.
-  // GSPLAT_SORT_SWEEP=0/1 forces one or the other.
-  bool sweep = !ctx->is_lane;
+  // The sort passes (radix_sort.cu) are single sweeps: 33 launches per frame instead of the 57 of the
+  // three-kernel passes.  How many CTAs a sweep gets is the per-context choice (profiles/ab_sort_r2.txt,
+  // 6 M bench frame): a frame that runs alone wants the whole GPU (3 CTAs per SM: sort A + B 0.340 ms
+  // against 0.394 with one per SM), but with several frames in flight the CTAs that wait in the
+  // look-back hold slots other lanes' kernels could use — 444 CTAs: 1574 frames/s, 148: 1637 (three-
+  // kernel passes: 1607).  GSPLAT_SORT_SWEEP=0 selects the three-kernel passes, GSPLAT_SORT_SWEEP_GRID
+  // sets the CTA count.
+  bool sweep = true;
   if (const char *e = std::getenv("GSPLAT_SORT_SWEEP")) sweep = std::atoi(e) != 0;
+  s.sweep_grid = ctx->is_lane ? 148u : (uint32_t)RS_GRID;
+  if (const char *e = std::getenv("GSPLAT_SORT_SWEEP_GRID")) s.sweep_grid = (uint32_t)std::max(1, std::atoi(e));
   if (sweep) {
     CU(cudaMalloc(&s.tile_state, (size_t)256 * s.max_tiles * sizeof(unsigned long long)));
     CU(cudaMemset(s.tile_state, 0, (size_t)256 * s.max_tiles * sizeof(unsigned long long)));

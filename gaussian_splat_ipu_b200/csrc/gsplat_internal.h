@@ -247,6 +247,7 @@ struct SortBuffers {
   // self-cleaning control block (RsSweepCtl); nullptr selects the three-kernel passes
   unsigned long long *tile_state;   // 256 * max_tiles
   uint32_t *sweep_ctl;              // RS_SWEEP_CTL_WORDS, zero at rest
+  uint32_t sweep_grid;              // CTAs of a single-sweep launch (0 = RS_GRID); tiles are handed out by ticket
 };
 // sweep_ctl layout (words): digit totals of every pass [RS_SWEEP_MAX_PASSES][256], then per pass a
 // tile ticket and an exit counter, then the sort serial number

@@ -601,6 +601,9 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
   const uint32_t grid = ntiles < (uint32_t)RS_GRID ? ntiles : (uint32_t)RS_GRID;
   if (sb.tile_state && sb.sweep_ctl && passes <= RS_SWEEP_MAX_PASSES) {
     // single-sweep form: the digit totals of all passes in one launch, then one launch per digit
+    // (tiles are handed out by ticket, so any grid works: sb.sweep_grid caps it)
+    const uint32_t grid_cap = sb.sweep_grid ? sb.sweep_grid : (uint32_t)RS_GRID;
+    const uint32_t sgrid = grid < grid_cap ? grid : grid_cap;
     ++g_launches;
     rs_hist_all_kernel<<<grid, RS_THREADS, 0, st>>>(sb.keys[0], d_n, sb.capacity, begin_bit, end_bit, bpp, passes,
                                                      sb.sweep_ctl, key_range);
@@ -610,14 +613,14 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
       const bool ident = p == 0 && identity_vals;
       ++g_launches;
       switch (bits) {
-        case 1: launch_sweep<1>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
-        case 2: launch_sweep<2>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
-        case 3: launch_sweep<3>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
-        case 4: launch_sweep<4>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
-        case 5: launch_sweep<5>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
-        case 6: launch_sweep<6>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
-        case 7: launch_sweep<7>(sb, cur, ident, d_n, shift, p, grid, key_range, st); break;
-        default: launch_sweep<8>(sb, cur, ident, d_n, shift, p, grid < 148u ? grid : 148u, key_range, st); break;
+        case 1: launch_sweep<1>(sb, cur, ident, d_n, shift, p, sgrid, key_range, st); break;
+        case 2: launch_sweep<2>(sb, cur, ident, d_n, shift, p, sgrid, key_range, st); break;
+        case 3: launch_sweep<3>(sb, cur, ident, d_n, shift, p, sgrid, key_range, st); break;
+        case 4: launch_sweep<4>(sb, cur, ident, d_n, shift, p, sgrid, key_range, st); break;
+        case 5: launch_sweep<5>(sb, cur, ident, d_n, shift, p, sgrid, key_range, st); break;
+        case 6: launch_sweep<6>(sb, cur, ident, d_n, shift, p, sgrid, key_range, st); break;
+        case 7: launch_sweep<7>(sb, cur, ident, d_n, shift, p, sgrid, key_range, st); break;
+        default: launch_sweep<8>(sb, cur, ident, d_n, shift, p, sgrid < 148u ? sgrid : 148u, key_range, st); break;
       }
       cur ^= 1;
     }
