@@ -17,17 +17,16 @@ timeout 300 python bench.py --mode bands --workload synthetic-6M-4k --steps 120 
 timeout 300 python bench.py --mode multiview --workload synthetic-3M-1080p --steps 5 --warmup 3 > $O/bench_cfg4_multiview_n1.json 2>> $O/bench.err
 timeout 200 python profiles/tile_profile.py synthetic-6M-1080p 3 > $O/tile_profile_6M.txt 2>&1
 # the captures run ONE frame at a time (one lane, fixed slicing): profiles/frames.py
-# (GSPLAT_SORT_SWEEP=0: the three-kernel sort passes, which is what the lanes of the bench's context run;
-#  the second list is the same frame with the single-sweep passes a one-frame-at-a-time context uses)
-export GSPLAT_SORT_SWEEP=0
+# launch list of the frame as every context runs it (single-sweep sort passes: 33 launches) and, for
+# comparison, with the three-kernel passes (GSPLAT_SORT_SWEEP=0: 57 launches)
 python profiles/frames.py > $O/frames.log 2>&1 || { tail -5 $O/frames.log; exit 1; }
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches.csv python profiles/frames.py > $O/ncu1.log 2>&1
-GSPLAT_SORT_SWEEP=1 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches_sweep.csv python profiles/frames.py > $O/ncu1b.log 2>&1
-# one frame (57 launches; 2 upload launches + frame 0 are skipped) + the next frame's K1, every section of the full set except the two that
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches_sweep.csv python profiles/frames.py > $O/ncu1.log 2>&1
+GSPLAT_SORT_SWEEP=0 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches.csv python profiles/frames.py > $O/ncu1b.log 2>&1
+# one frame (33 launches; 2 upload launches + frame 0 are skipped) + the next frame's K1, every section of the full set except the two that
 # store per-instruction / per-sample data for each of the 58 launches (SourceCounters, PmSampling):
 # gpurun brings back at most 64 MiB.  K5 alone is then captured with the whole --set full and its source.
 SECTIONS="--section ComputeWorkloadAnalysis --section InstructionStats --section LaunchStats --section MemoryWorkloadAnalysis --section MemoryWorkloadAnalysis_Tables --section Occupancy --section SchedulerStats --section SpeedOfLight --section WarpStateStats --section WorkloadDistribution"
-timeout 900 ncu $SECTIONS --metrics smsp__thread_inst_executed_per_inst_executed.ratio,sm__inst_issued.avg.pct_of_peak_sustained_active --clock-control none --launch-skip 59 --launch-count 58 -f -o $O/prof_frame python profiles/frames.py synthetic-6M-1080p 3 > $O/ncu2.log 2>&1
+timeout 900 ncu $SECTIONS --metrics smsp__thread_inst_executed_per_inst_executed.ratio,sm__inst_issued.avg.pct_of_peak_sustained_active --clock-control none --launch-skip 35 --launch-count 34 -f -o $O/prof_frame python profiles/frames.py synthetic-6M-1080p 3 > $O/ncu2.log 2>&1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:blend_kernel --launch-skip 2 --launch-count 2 -f -o $O/prof_blend python profiles/frames.py synthetic-6M-1080p 3 > $O/ncu3.log 2>&1
 # never lose the pass to the size limit: keep the raw page instead of the report if it is too large
 if [ $(du -sm gpurun_out | cut -f1) -gt 58 ]; then

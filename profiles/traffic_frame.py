@@ -43,10 +43,13 @@ STAGES = [("k1_project", r"project_kernel|tile_count|depth_quantile"), ("k3a_sor
 # rs_scan_kernel carries no digit width: it belongs to the sort whose kernels surround it
 kern, stages, last_sort = {}, {}, "k3a_sort_depth"
 pipes_acc = {}
-for name, by, us, extra in frame:
+for idx, (name, by, us, extra) in enumerate(frame):
     k = kern.setdefault(name, {"launches": 0, "dram_bytes": 0.0, "us": 0.0})
     k["launches"] += 1; k["dram_bytes"] += by; k["us"] += us
     st = next((s for s, pat in STAGES if re.search(pat, name)), None)
+    if name.startswith("rs_hist_all"):   # all-digit histogram of a single-sweep sort: it belongs to the sweeps behind it
+        nxt = next((n for n, _, _, _ in frame[idx + 1:] if n.startswith("rs_sweep")), "")
+        st = next((s for s, pat in STAGES if re.search(pat, nxt)), None)
     if name.startswith("rs_scan"):
         st = last_sort
     elif st in ("k3a_sort_depth", "k3b_sort_tile") and name.startswith("rs_"):
