@@ -359,12 +359,27 @@ __device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned l
 // rs_sweep_kernel skips them.
 __global__ void __launch_bounds__(RS_THREADS)
 rs_hist_all_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ d_n, uint32_t cap, int begin_bit,
-                   int end_bit, int bpp, int passes, uint32_t *__restrict__ ctl, const uint32_t *__restrict__ key_range) {
+                   int end_bit, int bpp, int passes, uint32_t *__restrict__ ctl, const uint32_t *__restrict__ key_range,
+                   unsigned long long *__restrict__ tile_state, size_t tile_words, uint32_t wrap_mask) {
   __shared__ uint32_t hist[RS_SWEEP_MAX_PASSES * 256];
+  __shared__ uint32_t wrapped;
   const uint32_t n = num_elems(d_n, cap);
   if (n == 0) return;
   const uint32_t tid = threadIdx.x;
-  if (blockIdx.x == 0 && tid == 0) ctl[RS_SWEEP_SERIAL] += 1u;     // read by the passes that follow
+  if (blockIdx.x == 0) {
+    // the sort's serial number, read by the passes that follow.  The look-back words carry it in 27
+    // bits (tag = serial * 8 + pass, 30 bits): long before a tag can come round again — every
+    // wrap_mask + 1 = 2^26 sorts, about a day of rendering — the words are wiped, here, before any
+    // pass of this sort runs, so a word of a sort 2^27 sorts ago can never be taken for a fresh one.
+    if (tid == 0) {
+      const uint32_t serial = ctl[RS_SWEEP_SERIAL] + 1u;
+      ctl[RS_SWEEP_SERIAL] = serial;
+      wrapped = (serial & wrap_mask) == 0u ? 1u : 0u;
+    }
+    __syncthreads();
+    if (wrapped)
+      for (size_t i = tid; i < tile_words; i += RS_THREADS) tile_state[i] = 0ull;
+  }
   const uint32_t ntiles = (uint32_t)(((uint64_t)n + RS_TILE - 1) / RS_TILE);
   if (blockIdx.x >= ntiles) return;
   const uint32_t kbits = key_range ? key_range_bits(key_range) : 32u;
@@ -605,8 +620,16 @@ int launch_radix_sort(SortBuffers &sb, const uint32_t *d_n, uint32_t n_upper, in
     const uint32_t grid_cap = sb.sweep_grid ? sb.sweep_grid : (uint32_t)RS_GRID;
     const uint32_t sgrid = grid < grid_cap ? grid : grid_cap;
     ++g_launches;
+    // GSPLAT_SORT_SERIAL_WRAP (tests): wipe the look-back words every that-many sorts instead of every 2^26
+    const uint32_t wrap_mask = [] {
+      const char *e = getenv("GSPLAT_SORT_SERIAL_WRAP");
+      uint32_t period = e ? (uint32_t)atoi(e) : 0u;
+      if (period < 2u || (period & (period - 1u))) period = 1u << 26;      // a power of two
+      return period - 1u;
+    }();
     rs_hist_all_kernel<<<grid, RS_THREADS, 0, st>>>(sb.keys[0], d_n, sb.capacity, begin_bit, end_bit, bpp, passes,
-                                                     sb.sweep_ctl, key_range);
+                                                     sb.sweep_ctl, key_range, sb.tile_state,
+                                                     (size_t)256 * sb.max_tiles, wrap_mask);
     for (int p = 0; p < passes; ++p) {
       const int shift = begin_bit + p * bpp;
       const int bits = (end_bit - shift) < bpp ? (end_bit - shift) : bpp;
