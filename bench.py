@@ -322,10 +322,11 @@ def stage_rooflines(tm, st, pairs, blended, W, H, tiles, clocks_mhz, peaks):
         # rect per Gaussian out; rect re-read by the counts
         "k1_project": 64 * N + 48 * V + 4 * N + 8 * N + 8 * N,
         # per slice: keys read by the selection (+ rect from the 2nd slice on), selected pairs written;
-        # per digit 4 B histogram read + 8 B read + 8 B write per selected Gaussian
-        "k3a_sort_depth": 4 * N * S + 8 * N * (S - 1) + 8 * A + 5 * 20 * A,
+        # single-sweep sort: one 4 B read of the keys for the digit totals of all passes, then per digit
+        # 8 B read + 8 B write per element (GSPLAT_SORT_SWEEP=0, the three-kernel passes: 20 B per digit)
+        "k3a_sort_depth": 4 * N * S + 8 * N * (S - 1) + 8 * A + (4 + 5 * 16) * A,
         "k2_duplicate": 4 * A + 8 * A + 8 * D,
-        "k3b_sort_tile": 20 * pb * D,
+        "k3b_sort_tile": (4 + 16 * pb) * D,
         "k4_ranges": 4 * D + 8 * tiles * S}
     out = {}
     for k, b in alg_bytes.items():
