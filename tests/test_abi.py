@@ -165,27 +165,20 @@ def test_group_host_compiles_and_group_arguments_are_checked(tmp_path):
     assert lib.gsplat_group_render_streamed(None, None) == -1 and lib.gsplat_group_size(None) == 0
 
 
-def test_host_only_synth_library_is_the_same_generator():
-    """libgsplat_synth.so (csrc/synth.cpp built with g++, no CUDA: what bench.py's CPU reference arm
-    loads so that it maps no product library) emits bit-identical records to gsplat_synth_scene of
-    the product library."""
-    from gaussian_splat_ipu_b200 import scene as sc
-    for n, seed in ((1, 1), (4097, 0xB2000006), (50000, 7)):
-        a, b = sc.synth_scene(n, seed), sp.synth_scene(n, seed)
-        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
-
-
-def test_reference_arm_does_not_map_the_product_library():
-    """bench.py --impl reference builds its scene without dlopen-ing libgsplat_b200.so."""
-    import subprocess
-    import sys
-    code = ("import sys; sys.argv=['bench.py','--impl','reference','--workload','synthetic-200k-720p','--steps','2','--warmup','1'];"
-            "import runpy\n"
-            "try:\n runpy.run_path('bench.py', run_name='__main__')\nexcept SystemExit: pass\n"
-            "maps=open('/proc/self/maps').read()\n"
-            "sys.stderr.write('MAPPED' if 'libgsplat_b200' in maps else 'CLEAN')")
-    r = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0 and r.stderr.strip().endswith("CLEAN"), r.stderr[-2000:]
+def test_static_sort_argument_errors_do_not_need_a_device():
+    """gsplat_sort_pairs_static checks its arguments before it touches a device: sizes beyond the static
+    scratch array, bit ranges, pointers."""
+    err = C.create_string_buffer(200)
+    f = sp.load_library().gsplat_sort_pairs_static
+    assert f(0, 256, 512, 768, 1024, sp.SORT_STATIC_MAX + 1, 0, 32, None, err, len(err)) == -3
+    assert b"GSPLAT_SORT_STATIC_MAX" in err.value and str(sp.SORT_STATIC_MAX).encode() in err.value
+    assert f(0, 256, 512, 768, 1024, 8, 4, 4, None, err, len(err)) == -1 and b"bit range" in err.value
+    assert f(0, 256, 512, 768, 1024, 8, 0, 33, None, err, len(err)) == -1
+    assert f(0, 0, 512, 768, 1024, 8, 0, 32, None, err, len(err)) == -1 and b"null" in err.value
+    assert f(0, 260, 512, 768, 1024, 8, 0, 32, None, err, len(err)) == -1 and b"aligned" in err.value
+    assert f(0, 256, 512, 256, 1024, 8, 0, 32, None, err, len(err)) == -1 and b"distinct" in err.value
+    assert f(0, 0, 0, 0, 0, 0, 0, 32, None, None, 0) == 0          # nothing to sort
+    assert f(0, 256, 512, 768, 1024, sp.SORT_STATIC_MAX + 1, 0, 32, None, None, 0) == -3   # no message buffer
 
 
 @pytest.mark.skipif(have_gpu(), reason="checks the no-GPU failure mode")
